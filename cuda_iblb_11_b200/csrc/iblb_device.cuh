@@ -1,0 +1,82 @@
+// Device-side data layout and kernel parameter blocks of libiblb (sm_100a only).
+//
+// Population storage (replaces the reference's AoS d_f/d_f0/d_f1/d_F of main.cu:469-483):
+//   ONE set of post-collision populations, double-buffered (A/B), structure-of-arrays,
+//   y-fastest:   f_i(xl, y)  at  base + i*plane + (xl + G)*ld + y,   xl in [-G, W+G)
+//   G ghost columns on each side hold the neighbouring slab's boundary columns (the slab's own
+//   opposite edge when one GPU owns the whole periodic channel), so the pull stencil never
+//   wraps an index.  ld (column pitch) is a multiple of 16 doubles, so every column is 128-byte
+//   aligned and a pair of rows (y0, y0+1), y0 even, is one 16-byte vector.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace iblb {
+
+// D2Q9 lattice of LatticeBoltzmann.cu:15-27, i = 0..8
+__device__ __constant__ const int kCx[9] = {0, 1, 0, -1, 0, 1, -1, -1, 1};
+__device__ __constant__ const int kCy[9] = {0, 0, 1, 0, -1, 1, 1, -1, -1};
+
+constexpr double kCs = 0.57735;  // device sound speed, LatticeBoltzmann.cu:11 (not 1/sqrt(3))
+constexpr int kMarkersPerCilium = 96;   // main.cu:83
+constexpr int kFinePoints = 9600;       // main.cu:81
+constexpr int kSpreadTileX = 8, kSpreadTileY = 32;
+
+struct Lattice {
+    int W;          // owned columns
+    int G;          // ghost columns per side
+    int YDIM;       // rows
+    int ld;         // column pitch in doubles
+    int XDIM;       // global channel width
+    int x0;         // global x of local column 0
+    long long plane;  // doubles per population plane = (W + 2G)*ld
+    __host__ __device__ long long off(int xl, int y) const {
+        return (long long)(xl + G) * ld + y;
+    }
+};
+
+// where a slab's outgoing boundary columns go: the neighbour's destination buffer
+struct Remote {
+    double *base;       // neighbour's population buffer (same A/B parity as our dst); may be ours
+    long long plane;    // its plane size
+    int ld, G, W;       // its pitch, ghost width and owned width
+};
+
+struct LbParams {
+    Lattice L;
+    const double *src;
+    double *dst;
+    Remote left, right;          // left neighbour's right ghosts / right neighbour's left ghosts
+    const double *band;          // IB force band [2][W][band_ld] (x then y fastest) or nullptr
+    int band_rows, band_ld;
+    double omega_plus, omega_minus;  // 1/TAU, 1/TAU2 (LatticeBoltzmann.cu:80-81)
+    double kforce;                   // 1 - 1/(2 TAU)  (LatticeBoltzmann.cu:56)
+    double gx, gy;                   // uniform body force
+    double half;                     // 0.5 when the half-force velocity applies, else 0
+    double *qacc;                    // per-warp running flux sums [YDIM/64] or nullptr
+    int xq;                          // local column of the flux plane (XDIM-5) or -1000
+    // columns this launch covers: c in [0, col_count) -> x = col_begin + c, and x += split_skip
+    // when x >= split_at (boundary launch = the first and last G columns in one grid)
+    int col_begin, col_count, split_at, split_skip;
+};
+
+struct MarkerArrays {
+    float2 *s, *u_s, *F_s;   // position, velocity, force per marker
+    int *eps;                // on/off switch
+    float2 *bbox;            // per cilium (min x, max x) of the wrapped positions
+};
+
+struct IbParams {
+    Lattice L;
+    const double *src;       // populations the step pulls from
+    MarkerArrays M;
+    const float *coef;       // [96][28] a_n(x,y), b_n(x,y), n = 0..6 per marker (main.cu:109-135)
+    int c_num, c_space, T, p_step, it;
+    int *it_ptr;             // when set, the iteration number lives on the device (CUDA graphs)
+    int Ns;
+    int r_max;               // main.cu:185
+    double *band;            // force band, see LbParams
+    int band_rows, band_ld;
+};
+
+}  // namespace iblb

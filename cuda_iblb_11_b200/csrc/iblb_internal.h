@@ -1,0 +1,76 @@
+// Host-side solver object behind the C ABI of include/iblb.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+
+#include "iblb.h"
+#include "iblb_device.cuh"
+
+namespace iblb {
+
+void set_error(const std::string &msg);
+int cuda_fail(cudaError_t e, const char *what);
+
+#define IBLB_CUDA(call)                                         \
+    do {                                                        \
+        cudaError_t e__ = (call);                               \
+        if (e__ != cudaSuccess) return cuda_fail(e__, #call);   \
+    } while (0)
+
+// kernels (lb_kernels.cu / ib_kernels.cu)
+__global__ void lb_fused_v2(const LbParams p);
+__global__ void lb_fused_v1(const LbParams p, double *qpart);
+__global__ void flux_reduce_v1(const double *qpart, int n, double *qacc);
+__global__ void lb_init(const LbParams p, const double *rho_in, const double *u_in, double u0_amp);
+__global__ void halo_push(const Lattice L, const double *buf, Remote left, Remote right);
+__global__ void lb_moments(const LbParams p, int streamed, double *rho_out, double *u_out,
+                           double *f_out, double *force_out);
+__global__ void ib_coef(const int *k_of_j, float *coef);
+__global__ void ib_kinematics(const IbParams p);
+__global__ void ib_interpolate(const IbParams p);
+__global__ void ib_spread(const IbParams p);
+__global__ void slab_wait(const volatile int *flag_l, const volatile int *flag_r, int need);
+__global__ void slab_signal(int *left_flag, int *right_flag, int value);
+
+}  // namespace iblb
+
+struct iblb_solver {
+    iblb_params p;
+    iblb::Lattice L;
+    int device;
+    bool vec2;                 // fast path usable (YDIM % 64 == 0)
+    double *buf[2];            // population buffers A/B
+    int cur;                   // buffer the NEXT step pulls from
+    unsigned it;               // completed iterations
+    // IB
+    int Ns;
+    iblb::MarkerArrays M;
+    float *coef;
+    int *k_of_j_dev;
+    std::vector<int> k_of_j;
+    double *band;
+    int band_rows, band_ld;
+    int *it_dev;               // device copy of `it` read by the graph-captured kinematics
+    // flux
+    double *qacc, *qpart;
+    int nq;
+    bool flux_on;
+    int xq_local;
+    // execution
+    cudaStream_t stream;
+    cudaEvent_t ev0, ev1;
+    bool timed;
+    cudaGraphExec_t graph_exec;  // two iterations (A->B, B->A), built lazily
+    unsigned long long last_launches;
+    // slab coupling
+    bool connected;
+    iblb::Remote nb[2][2];     // [face 0=left,1=right][buffer parity]
+    void *nb_mapped[2][2];
+    int *flags;                // [0]: written by the left neighbour, [1]: by the right one
+    int *nb_flag[2];           // left neighbour's flags[1], right neighbour's flags[0]
+    void *nb_flag_mapped[2];
+    bool self_left, self_right;
+    iblb_solver *peer[2];      // same-process neighbours (iblb_connect_local)
+    cudaEvent_t ev_boundary;   // recorded after this slab's boundary-column kernel
+};

@@ -1,0 +1,412 @@
+// Fused pull-stream + moments + TRT collide + Guo forcing for D2Q9/FP64 on sm_100a.
+//
+// One launch replaces the reference's chain  streaming -> macro -> [spread's velocity update] ->
+// equilibrium -> collision  (LatticeBoltzmann.cu:173-373, 375-411; ImmersedBoundary.cu:249-264;
+// LatticeBoltzmann.cu:30-62, 64-136): only post-collision populations live in HBM between steps,
+// 144 B per lattice update (9 doubles read + 9 written) against the reference's ~816 B.
+//
+// Mapping: one thread owns two vertically adjacent nodes (y0, y0+1) of one column, one warp owns
+// 64 consecutive rows.  Every population is fetched with ONE aligned 128-bit load per thread
+// from the column it streams from (x - c_x); the +-1 row shift of the six populations with
+// c_y != 0 is done in registers with a warp shuffle, and only lane 0 / lane 31 issue one extra
+// 8-byte load each for the value that comes from the neighbouring warp's rows.  The walls are
+// folded into that edge load: at y = 0 the three upward populations are the node's own
+// downward ones (half-way bounce-back, LatticeBoltzmann.cu:231,287-291,309-313,328-340), at
+// y = YDIM-1 the three downward ones are the node's own upward ones mirrored in y only
+// (specular, LatticeBoltzmann.cu:225,243-247,265-269,341-353).  x-periodicity / slab coupling
+// costs nothing: ghost columns hold the neighbour's values and the threads of the boundary
+// columns store their results a second time into the neighbour's ghost columns (a peer
+// pointer over NVLink when the neighbour is another GPU).
+#include "iblb_device.cuh"
+
+namespace iblb {
+
+namespace {
+
+constexpr double kIcs2 = 1.0 / (kCs * kCs);                     // 1/cs^2
+constexpr double kIcs4 = 1.0 / (kCs * kCs * kCs * kCs);         // 1/cs^4
+constexpr double kIcs4h = 1.0 / (2.0 * kCs * kCs * kCs * kCs);  // 1/(2 cs^4)
+constexpr double kIcs2h = 1.0 / (2.0 * kCs * kCs);              // 1/(2 cs^2)
+constexpr double kW0 = 4.0 / 9.0, kW1 = 1.0 / 9.0, kW2 = 1.0 / 36.0;
+
+// reflection partners used by the wall rules (pull form)
+//   y == 0      : f2 <- f4, f5 <- f7, f6 <- f8   (same node)
+//   y == YDIM-1 : f4 <- f2, f7 <- f6, f8 <- f5   (same node)
+
+__device__ __forceinline__ double shfl_up1(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
+__device__ __forceinline__ double shfl_dn1(double v) {
+    return __shfl_down_sync(0xffffffffu, v, 1);
+}
+
+__device__ __forceinline__ double2 ldg2(const double *p) {
+    return __ldg(reinterpret_cast<const double2 *>(p));
+}
+
+// TRT relaxation of one antiparallel pair (a = +c, b = -c) plus the Guo term.
+// LatticeBoltzmann.cu:88-134 with f0 split into its even/odd parts analytically.
+__device__ __forceinline__ void relax_pair(double &fa, double &fb, double rw, double cu,
+                                           double base, double wp, double wm, double kw,
+                                           double cF, double uF, bool forced) {
+    const double f0p = rw * (base + cu * cu * kIcs4h);
+    const double f0m = rw * (cu * kIcs2);
+    const double fp = 0.5 * (fa + fb);
+    const double fm = 0.5 * (fa - fb);
+    const double A = wp * (fp - f0p);
+    const double B = wm * (fm - f0m);
+    double na = fa - A - B;
+    double nb = fb - A + B;
+    if (forced) {
+        const double S = kw * (cu * cF * kIcs4 - uF * kIcs2);
+        const double D = kw * (cF * kIcs2);
+        na += S + D;
+        nb += S - D;
+    }
+    fa = na;
+    fb = nb;
+}
+
+// moments (LatticeBoltzmann.cu:396-405, summation order i = 0..8), half-force velocity
+// (ImmersedBoundary.cu:249-255), then equilibrium + forcing + TRT.  Returns u_x.
+__device__ __forceinline__ double collide_node(double (&f)[9], double Fx, double Fy, bool forced,
+                                               const LbParams &p) {
+    const double rho = f[0] + f[1] + f[2] + f[3] + f[4] + f[5] + f[6] + f[7] + f[8];
+    const double mx = f[1] - f[3] + f[5] - f[6] - f[7] + f[8];
+    const double my = f[2] - f[4] + f[5] + f[6] - f[7] - f[8];
+    const double ir = 1.0 / rho;
+    const double ux = (mx + p.half * Fx) * ir;
+    const double uy = (my + p.half * Fy) * ir;
+    const double base = 1.0 - (ux * ux + uy * uy) * kIcs2h;
+    const double wp = p.omega_plus, wm = p.omega_minus;
+    const double uF = ux * Fx + uy * Fy;
+    const double k1 = p.kforce * kW1, k2 = p.kforce * kW2;
+    const double r1 = rho * kW1, r2 = rho * kW2;
+    // rest population: no force term (LatticeBoltzmann.cu:86)
+    f[0] = f[0] - wp * (f[0] - rho * kW0 * base);
+    relax_pair(f[1], f[3], r1, ux, base, wp, wm, k1, Fx, uF, forced);
+    relax_pair(f[2], f[4], r1, uy, base, wp, wm, k1, Fy, uF, forced);
+    relax_pair(f[5], f[7], r2, ux + uy, base, wp, wm, k2, Fx + Fy, uF, forced);
+    relax_pair(f[6], f[8], r2, uy - ux, base, wp, wm, k2, Fy - Fx, uF, forced);
+    return ux;
+}
+
+__device__ __forceinline__ void store_remote2(const Remote &r, int col, int y0, int i, double2 v) {
+    *reinterpret_cast<double2 *>(r.base + (long long)i * r.plane + (long long)(col + r.G) * r.ld +
+                                 y0) = v;
+}
+
+}  // namespace
+
+// Fast path: YDIM % 64 == 0.  grid = ceil(W*YDIM/2 / 256), block = 256.
+__global__ void __launch_bounds__(256, 3) lb_fused_v2(const LbParams p) {
+    const Lattice &L = p.L;
+    const int HP = L.YDIM >> 1;  // row pairs per column (multiple of 32: warps never straddle)
+    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (long long)p.col_count * HP) return;  // whole warps only
+    const int c = (int)(gid / HP);
+    const int yp = (int)(gid - (long long)c * HP);
+    int x = p.col_begin + c;
+    if (x >= p.split_at) x += p.split_skip;
+    const int y0 = yp << 1;
+    const int lane = threadIdx.x & 31;
+    const bool at_bottom = (y0 == 0);
+    const bool at_top = (y0 + 2 == L.YDIM);
+
+    const double *__restrict__ src = p.src;
+    const long long P = L.plane;
+    const long long cm = L.off(x - 1, y0), c0 = L.off(x, y0), cp = L.off(x + 1, y0);
+
+    // ---- all loads first: 9 aligned 128-bit loads per thread ----
+    const double2 v0 = ldg2(src + 0 * P + c0);
+    const double2 v1 = ldg2(src + 1 * P + cm);  // c = (+1, 0): from x-1
+    const double2 v2 = ldg2(src + 2 * P + c0);  // c = ( 0,+1): from y-1
+    const double2 v3 = ldg2(src + 3 * P + cp);  // c = (-1, 0): from x+1
+    const double2 v4 = ldg2(src + 4 * P + c0);  // c = ( 0,-1): from y+1
+    const double2 v5 = ldg2(src + 5 * P + cm);  // c = (+1,+1)
+    const double2 v6 = ldg2(src + 6 * P + cp);  // c = (-1,+1)
+    const double2 v7 = ldg2(src + 7 * P + cp);  // c = (-1,-1)
+    const double2 v8 = ldg2(src + 8 * P + cm);  // c = (+1,-1)
+    // edge values for the row below lane 0 / above lane 31 (walls folded in)
+    double e2 = 0., e5 = 0., e6 = 0., e4 = 0., e7 = 0., e8 = 0.;
+    if (lane == 0) {
+        if (at_bottom) {
+            e2 = v4.x;  // f2(x,0) <- f4(x,0): already loaded (same column, row y0)
+            e5 = __ldg(src + 7 * P + c0);
+            e6 = __ldg(src + 8 * P + c0);
+        } else {
+            e2 = __ldg(src + 2 * P + c0 - 1);
+            e5 = __ldg(src + 5 * P + cm - 1);
+            e6 = __ldg(src + 6 * P + cp - 1);
+        }
+    }
+    if (lane == 31) {
+        if (at_top) {
+            e4 = v2.y;  // f4(x,Y-1) <- f2(x,Y-1)
+            e7 = __ldg(src + 6 * P + c0 + 1);
+            e8 = __ldg(src + 5 * P + c0 + 1);
+        } else {
+            e4 = __ldg(src + 4 * P + c0 + 2);
+            e7 = __ldg(src + 7 * P + cp + 2);
+            e8 = __ldg(src + 8 * P + cm + 2);
+        }
+    }
+    // force: IB band (rows < band_rows) + uniform body force
+    double Fx0 = p.gx, Fy0 = p.gy, Fx1 = p.gx, Fy1 = p.gy;
+    bool forced = (p.gx != 0.0) | (p.gy != 0.0);
+    if (p.band != nullptr && y0 < p.band_rows) {  // warp-uniform: band_rows % 64 == 0
+        const double *b = p.band + (long long)x * p.band_ld + y0;
+        const double2 bx = ldg2(b);
+        const double2 by = ldg2(b + (long long)L.W * p.band_ld);
+        Fx0 += bx.x; Fx1 += bx.y; Fy0 += by.x; Fy1 += by.y;
+        forced = true;
+    }
+
+    // ---- shift the six populations with c_y != 0 by one row in registers ----
+    double a[9], b[9];  // node y0, node y0+1
+    a[0] = v0.x; b[0] = v0.y;
+    a[1] = v1.x; b[1] = v1.y;
+    a[3] = v3.x; b[3] = v3.y;
+    {
+        double t;
+        t = shfl_up1(v2.y); a[2] = lane == 0 ? e2 : t; b[2] = v2.x;
+        t = shfl_up1(v5.y); a[5] = lane == 0 ? e5 : t; b[5] = v5.x;
+        t = shfl_up1(v6.y); a[6] = lane == 0 ? e6 : t; b[6] = v6.x;
+        t = shfl_dn1(v4.x); a[4] = v4.y; b[4] = lane == 31 ? e4 : t;
+        t = shfl_dn1(v7.x); a[7] = v7.y; b[7] = lane == 31 ? e7 : t;
+        t = shfl_dn1(v8.x); a[8] = v8.y; b[8] = lane == 31 ? e8 : t;
+    }
+
+    const double ux0 = collide_node(a, Fx0, Fy0, forced, p);
+    const double ux1 = collide_node(b, Fx1, Fy1, forced, p);
+
+    // ---- 9 aligned 128-bit stores ----
+    double *__restrict__ dst = p.dst;
+#pragma unroll
+    for (int i = 0; i < 9; i++)
+        *reinterpret_cast<double2 *>(dst + i * P + c0) = make_double2(a[i], b[i]);
+
+    // boundary columns: second copy into the neighbours' ghost columns (block-uniform per warp)
+    if (x < p.left.G) {
+#pragma unroll
+        for (int i = 0; i < 9; i++)
+            store_remote2(p.left, p.left.W + x, y0, i, make_double2(a[i], b[i]));
+    }
+    if (x >= L.W - p.right.G) {
+#pragma unroll
+        for (int i = 0; i < 9; i++)
+            store_remote2(p.right, x - L.W, y0, i, make_double2(a[i], b[i]));
+    }
+
+    // flux through the plane x = XDIM-5 (ImmersedBoundary.cu:259-264): fixed-order warp tree,
+    // one running sum per warp slot, summed on the host in slot order => deterministic
+    if (x == p.xq && p.qacc != nullptr) {
+        double q = ux0 + ux1;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) q += __shfl_down_sync(0xffffffffu, q, o);
+        if (lane == 0) p.qacc[yp >> 5] += q / (double)L.YDIM;
+    }
+}
+
+// Generic path: any YDIM >= 2, one node per thread, scalar loads.  Same arithmetic.
+__global__ void __launch_bounds__(256) lb_fused_v1(const LbParams p, double *qpart) {
+    const Lattice &L = p.L;
+    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool active = gid < (long long)p.col_count * L.YDIM;
+    int x = 0, y = 0;
+    double ux = 0.;
+    if (active) {
+        const int c = (int)(gid / L.YDIM);
+        y = (int)(gid - (long long)c * L.YDIM);
+        x = p.col_begin + c;
+        if (x >= p.split_at) x += p.split_skip;
+        const double *__restrict__ src = p.src;
+        const long long P = L.plane;
+        double f[9];
+#pragma unroll
+        for (int i = 0; i < 9; i++) {
+            int pi = i, xs = x - kCx[i], ys = y - kCy[i];
+            if (ys < 0) {  // bottom wall: own opposite population
+                pi = (i == 2) ? 4 : (i == 5) ? 7 : 8;
+                xs = x; ys = y;
+            } else if (ys >= L.YDIM) {  // top wall: own y-mirrored population
+                pi = (i == 4) ? 2 : (i == 7) ? 6 : 5;
+                xs = x; ys = y;
+            }
+            f[i] = __ldg(src + pi * P + L.off(xs, ys));
+        }
+        double Fx = p.gx, Fy = p.gy;
+        bool forced = (p.gx != 0.0) | (p.gy != 0.0);
+        if (p.band != nullptr && y < p.band_rows) {
+            const double *b = p.band + (long long)x * p.band_ld + y;
+            Fx += __ldg(b);
+            Fy += __ldg(b + (long long)L.W * p.band_ld);
+            forced = true;
+        }
+        ux = collide_node(f, Fx, Fy, forced, p);
+        const long long c0 = L.off(x, y);
+#pragma unroll
+        for (int i = 0; i < 9; i++) p.dst[i * P + c0] = f[i];
+        if (x < p.left.G) {
+#pragma unroll
+            for (int i = 0; i < 9; i++)
+                p.left.base[(long long)i * p.left.plane +
+                            (long long)(p.left.W + x + p.left.G) * p.left.ld + y] = f[i];
+        }
+        if (x >= L.W - p.right.G) {
+#pragma unroll
+            for (int i = 0; i < 9; i++)
+                p.right.base[(long long)i * p.right.plane +
+                             (long long)(x - L.W + p.right.G) * p.right.ld + y] = f[i];
+        }
+    }
+    // flux: per-node values of the flux column go to a scratch column, reduced by flux_reduce_v1
+    if (active && x == p.xq && qpart != nullptr) qpart[y] = ux / (double)L.YDIM;
+}
+
+// generic path's deterministic flux reduction: one block, fixed strided order + fixed tree
+__global__ void flux_reduce_v1(const double *qpart, int n, double *qacc) {
+    __shared__ double sh[256];
+    double v = 0.;
+    for (int y = threadIdx.x; y < n; y += 256) v += qpart[y];
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) qacc[0] += sh[0];
+}
+
+// ---------------------------------------------------------------------------------------------
+// Initial state (main.cu:636-654, 722-754): f = f0(rho,u); stored post-collision:
+// f* = f0 + F(u, g) because TRT leaves an equilibrium unchanged.  rho/u come from device arrays
+// in the reference layout (j = y*W + x) or, when null, rho = 1, u_x = u0_amp*sin(2pi(y+.5)/Y).
+__global__ void lb_init(const LbParams p, const double *rho_in, const double *u_in, double u0_amp) {
+    const Lattice &L = p.L;
+    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (long long)L.W * L.YDIM) return;
+    const int x = (int)(gid / L.YDIM), y = (int)(gid - (long long)x * L.YDIM);
+    double rho = 1.0, ux, uy = 0.0;
+    const double kTwoPi = 6.283185307179586476925286766559;
+    if (rho_in != nullptr) {
+        const long long j = (long long)y * L.W + x, size = (long long)L.W * L.YDIM;
+        rho = rho_in[j];
+        ux = u_in[j];
+        uy = u_in[size + j];
+    } else {
+        ux = u0_amp * sin(kTwoPi * (y + 0.5) / L.YDIM);
+    }
+    const double w[9] = {kW0, kW1, kW1, kW1, kW1, kW2, kW2, kW2, kW2};
+    const double cs2 = kCs * kCs;
+    const long long c0 = L.off(x, y);
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+        const double cx = kCx[i], cy = kCy[i];
+        const double cu = ux * cx + uy * cy;
+        // LatticeBoltzmann.cu:47-50 / :53-56 evaluated as written
+        double f0 = rho * w[i] *
+                    (1 + cu / cs2 + cu * cu / (2 * cs2 * cs2) - (ux * ux + uy * uy) / (2 * cs2));
+        if (i > 0) {
+            const double vx = (cx - ux) / cs2 + cu / (cs2 * cs2) * cx;
+            const double vy = (cy - uy) / cs2 + cu / (cs2 * cs2) * cy;
+            f0 += p.kforce * w[i] * (vx * p.gx + vy * p.gy);
+        }
+        p.dst[i * L.plane + c0] = f0;
+    }
+}
+
+// copy the owned boundary columns of `buf` into the neighbours' ghost columns (used after init;
+// the fused kernel does this itself every step)
+__global__ void halo_push(const Lattice L, const double *buf, Remote left, Remote right) {
+    const int y = blockIdx.x * blockDim.x + threadIdx.x;
+    const int g = blockIdx.y;  // ghost column index
+    const int i = blockIdx.z;
+    if (y >= L.YDIM) return;
+    if (g < left.G) {
+        left.base[(long long)i * left.plane + (long long)(left.W + g + left.G) * left.ld + y] =
+            buf[i * L.plane + L.off(g, y)];
+    }
+    if (g < right.G) {
+        right.base[(long long)i * right.plane + (long long)(g - right.G + right.G) * right.ld + y] =
+            buf[i * L.plane + L.off(L.W - right.G + g, y)];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Macroscopic fields / streamed populations of the last completed iteration, recomputed from the
+// buffer that iteration pulled from (still intact: the step wrote the other buffer).  Output in
+// the reference layouts.  `streamed` false = iteration 0 (no step yet): local moments.
+__global__ void lb_moments(const LbParams p, int streamed, double *rho_out, double *u_out,
+                           double *f_out, double *force_out) {
+    const Lattice &L = p.L;
+    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long size = (long long)L.W * L.YDIM;
+    if (gid >= size) return;
+    // x fastest here so that the reference-layout stores coalesce
+    const int y = (int)(gid / L.W), x = (int)(gid - (long long)y * L.W);
+    const long long P = L.plane;
+    double f[9];
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+        int pi = i, xs = x, ys = y;
+        if (streamed) {
+            xs = x - kCx[i];
+            ys = y - kCy[i];
+            if (ys < 0) {
+                pi = (i == 2) ? 4 : (i == 5) ? 7 : 8;
+                xs = x; ys = y;
+            } else if (ys >= L.YDIM) {
+                pi = (i == 4) ? 2 : (i == 7) ? 6 : 5;
+                xs = x; ys = y;
+            }
+        }
+        f[i] = p.src[pi * P + L.off(xs, ys)];
+    }
+    double Fx = 0., Fy = 0.;
+    if (p.band != nullptr && y < p.band_rows) {
+        Fx = p.band[(long long)x * p.band_ld + y];
+        Fy = p.band[(long long)(L.W + x) * p.band_ld + y];
+    }
+    if (p.half != 0.0 || p.band != nullptr) { /* force array as `spread` leaves it */ }
+    const double rho = f[0] + f[1] + f[2] + f[3] + f[4] + f[5] + f[6] + f[7] + f[8];
+    const double mx = f[1] - f[3] + f[5] - f[6] - f[7] + f[8];
+    const double my = f[2] - f[4] + f[5] + f[6] - f[7] - f[8];
+    if (rho_out) rho_out[gid] = rho;
+    if (u_out) {
+        u_out[gid] = (mx + p.half * (Fx + p.gx)) / rho;
+        u_out[size + gid] = (my + p.half * (Fy + p.gy)) / rho;
+    }
+    if (f_out) {
+#pragma unroll
+        for (int i = 0; i < 9; i++) f_out[9 * gid + i] = f[i];
+    }
+    if (force_out) {
+        force_out[gid] = Fx + p.gx;
+        force_out[size + gid] = Fy + p.gy;
+    }
+}
+
+}  // namespace iblb
+
+namespace iblb {
+
+// ---- slab ordering across GPUs (one process per GPU): step counters in peer-mapped memory.
+// The waiting side spins on ITS OWN memory; the writer is a kernel on another GPU, so both are
+// always resident (never used between ranks that share a GPU).
+__global__ void slab_wait(const volatile int *flag_l, const volatile int *flag_r, int need) {
+    if (threadIdx.x == 0) {
+        while (*flag_l < need) __nanosleep(100);
+        while (*flag_r < need) __nanosleep(100);
+        __threadfence_system();
+    }
+}
+
+__global__ void slab_signal(int *left_flag, int *right_flag, int value) {
+    if (threadIdx.x == 0) {
+        __threadfence_system();  // the boundary kernel's peer stores are ordered before the flag
+        *reinterpret_cast<volatile int *>(left_flag) = value;
+        *reinterpret_cast<volatile int *>(right_flag) = value;
+        __threadfence_system();
+    }
+}
+
+}  // namespace iblb

@@ -1,0 +1,208 @@
+// Driver-level run: what the reference's main() does around the time-step loop — the Data/ tree,
+// SimLog.txt, the flux file, and (BigData) the fluid/cilia snapshots.  Replaces main.cu:589-631,
+// 758-790, 936-1005, 1030-1060.  Pure host C++ on top of the C ABI; the numbers go through
+// default-formatted ostreams exactly as in the reference, so the text matches digit for digit.
+#include <sys/stat.h>
+#include <sys/types.h>
+
+#include <chrono>
+#include <cmath>
+#include <cstdlib>
+#include <ctime>
+#include <fstream>
+#include <iomanip>
+#include <iostream>
+#include <sstream>
+#include <string>
+#include <vector>
+
+#include "iblb.h"
+
+namespace iblb {
+void set_error(const std::string &msg);
+}
+
+namespace {
+
+// main.cu:255-261
+template <typename T>
+std::string to_string_3(const T v, const int n = 3) {
+    std::ostringstream out;
+    out << std::setprecision(n) << v;
+    return out.str();
+}
+
+void mkdir_p(const std::string &path) {
+    std::string cur;
+    for (size_t i = 0; i < path.size(); i++) {
+        cur += path[i];
+        if (path[i] == '/' || i + 1 == path.size()) mkdir(cur.c_str(), 0777);
+    }
+}
+
+double now_seconds() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch())
+        .count();
+}
+
+}  // namespace
+
+extern "C" int iblb_run(const iblb_params *pp, const char *root) {
+    using namespace std;
+    if (!pp) return IBLB_EINVAL;
+    iblb_params p = *pp;
+    const unsigned XDIM = p.XDIM, YDIM = p.YDIM, c_num = p.c_num, c_fraction = p.c_fraction;
+    const unsigned ITERATIONS = p.ITERATIONS, INTERVAL = p.INTERVAL;
+    const size_t size = (size_t)XDIM * YDIM;
+    const int Ns = 96 * (int)c_num;
+
+    // ---- directories, main.cu:589-613 (root is configurable; the reference hard-codes it) ----
+    string output_data = root ? root : "Data/";
+    if (!output_data.empty() && output_data.back() != '/') output_data += '/';
+    string raw_data = output_data + "Raw/" + to_string(c_num) + "/" + to_string(c_fraction) + "/";
+    string cilia_data = output_data + "Cilia/" + to_string(c_num) + "/" + to_string(c_fraction) + "/";
+    mkdir_p(raw_data);
+    mkdir_p(cilia_data);
+    mkdir_p(output_data + "Flux/");
+    string flux = output_data + "/Flux/" + to_string(c_fraction) + "_" + to_string(c_num) + "_" +
+                  to_string(p.c_space) + "_" + to_string_3(p.Re) + "_" + to_string_3(p.T_num) +
+                  "x" + to_string_3(p.T_pow) + "-flux.dat";
+    string parameters = raw_data + "/SimLog.txt";
+
+    ofstream fsA, fsB, fsC;
+    fsB.open(flux.c_str(), ofstream::trunc);
+    if (!fsB) {
+        iblb::set_error("cannot write " + flux);
+        return IBLB_EIO;
+    }
+    fsB.close();
+
+    time_t rawtime;
+    time(&rawtime);
+    struct tm *timeinfo = localtime(&rawtime);
+    cout << asctime(timeinfo) << endl;
+    cout << "Initialising...\n";
+
+    iblb_solver *s = nullptr;
+    int rc = iblb_create(&p, &s);
+    if (rc) return rc;
+
+    // ---- SimLog header, main.cu:761-790 ----
+    const double l_0 = 0.000006, t_0 = 0.067;
+    const double dx = 1. / p.LENGTH, dt = 1. / p.T;
+    fsC.open(parameters.c_str(), ofstream::trunc);
+    fsC << asctime(timeinfo) << endl;
+    fsC << "Size: " << XDIM << "x" << YDIM << endl;
+    fsC << "Iterations: " << ITERATIONS << endl;
+    fsC << "Reynolds Number: " << p.Re << endl;
+    fsC << "Relaxation times: " << p.TAU << ", " << p.TAU2 << endl;
+    fsC << "Spatial step: " << dx * l_0 << "m" << endl;
+    fsC << "Time step: " << dt * t_0 << "s" << endl;
+    fsC << "Mach number: " << p.Ma << endl;
+    fsC << "Phase Step: " << c_fraction << "/" << c_num << endl;
+    if (p.BigData) fsC << "\nBig Data is ON" << endl;
+    else fsC << "\nBig Data is OFF" << endl;
+    if (p.ShARC) fsC << "Running on ShARC" << endl;
+    else fsC << "Running on local GPU" << endl;
+
+    cout << "Running Simulation...\n";
+    const double start = now_seconds();
+
+    vector<double> rho, u;
+    vector<float> sm, us;
+    vector<int> eps;
+    if (p.BigData) {
+        rho.resize(size);
+        u.resize(2 * size);
+        sm.resize(2 * (size_t)Ns + 2);
+        us.resize(2 * (size_t)Ns + 2);
+        eps.resize((size_t)Ns + 1);
+    }
+
+    // iteration `it` (0-based) is complete after it+1 steps; outputs follow iterations with
+    // it % INTERVAL == 0 (main.cu:938); everything in between runs without host involvement
+    unsigned done = 0;
+    while (done < ITERATIONS && rc == IBLB_OK) {
+        unsigned it_out;  // next iteration index whose completion triggers output
+        if (INTERVAL == 0) it_out = ITERATIONS;  // no periodic output
+        else it_out = ((done + INTERVAL - 1) / INTERVAL) * INTERVAL;
+        unsigned target = (it_out < ITERATIONS) ? it_out + 1 : ITERATIONS;
+        rc = iblb_step(s, target - done);
+        if (rc) break;
+        done = target;
+        const unsigned it = done - 1;
+        if (INTERVAL != 0 && it % INTERVAL == 0) {
+            if (p.BigData) {
+                rc = iblb_get_fields(s, rho.data(), u.data());
+                if (rc) break;
+                string outfile = raw_data + to_string(it) + "-fluid.dat";
+                fsA.open(outfile.c_str());
+                for (size_t j = 0; j < size; j++) {  // main.cu:958-969
+                    const int x = (int)(j % XDIM);
+                    const int y = (int)((j - j % XDIM) / XDIM);
+                    const double ab = sqrt(u[j] * u[j] + u[size + j] * u[size + j]);
+                    fsA << x * p.x_scale << "\t" << y * p.x_scale << "\t" << u[j] * p.s_scale
+                        << "\t" << u[size + j] * p.s_scale << "\t" << ab * p.s_scale << "\t"
+                        << rho[j] << endl;
+                    if (x == (int)XDIM - 1) fsA << endl;
+                }
+                fsA.close();
+                rc = iblb_get_markers(s, sm.data(), us.data(), nullptr, eps.data());
+                if (rc) break;
+                outfile = cilia_data + to_string(it) + "-cilia.dat";
+                fsA.open(outfile.c_str());
+                for (int k = 0; k < Ns; k++) {  // main.cu:986-992
+                    fsA << sm[2 * k + 0] * p.x_scale << "\t" << sm[2 * k + 1] * p.x_scale << "\t"
+                        << us[2 * k + 0] * p.s_scale << "\t" << us[2 * k + 1] * p.s_scale << "\t"
+                        << eps[k] << "\n";
+                    if (k % 96 == 95 || sm[2 * k + 0] > XDIM - 1 || sm[2 * k + 0] < 1) fsA << "\n";
+                }
+                fsA.close();
+            }
+            double Q = 0.;
+            rc = iblb_get_flux(s, &Q);
+            if (rc) break;
+            fsB.open(flux.c_str(), ofstream::app);
+            fsB << it * p.t_scale << "\t" << Q * p.x_scale << endl;  // main.cu:1002
+            fsB.close();
+        }
+        if (it == INTERVAL && INTERVAL != 0) {  // main.cu:1007-1022
+            const double cycle = now_seconds();
+            time_t p_runtime = (time_t)((cycle - start) * (ITERATIONS / INTERVAL));
+            time_t p_end = rawtime + p_runtime;
+            timeinfo = localtime(&p_end);
+            cout << "\nCompletion time: " << asctime(timeinfo) << endl;
+            fsC << "\nCompletion time: " << asctime(timeinfo) << endl;
+            fsC.close();
+        }
+    }
+    if (rc == IBLB_OK) {
+        double Q = 0.;
+        rc = iblb_get_flux(s, &Q);
+        fsB.open(flux.c_str(), ofstream::app);
+        fsB << ITERATIONS * p.t_scale << "\t" << Q * p.x_scale << endl;  // main.cu:1030-1034
+        fsB.close();
+    }
+    string keep = iblb_last_error();
+    iblb_sync(s);
+    const double runtime = now_seconds() - start;  // main.cu:1038-1057
+    int hours = 0, mins = 0;
+    if (runtime > 3600) hours = (int)nearbyint(runtime / 3600 - 0.5);
+    if (runtime > 60) mins = (int)nearbyint((runtime - hours * 3600) / 60 - 0.5);
+    const double secs = runtime - hours * 3600 - mins * 60;
+    if (fsC.is_open()) fsC.close();
+    fsC.open(parameters.c_str(), ofstream::app);
+    fsC << "Total runtime: ";
+    if (hours < 10) fsC << 0;
+    fsC << hours << ":";
+    if (mins < 10) fsC << 0;
+    fsC << mins << ":";
+    if (secs < 10) fsC << 0;
+    fsC << secs << endl;
+    // additions of this implementation (after the reference's last line)
+    fsC << "MLUPS: " << (runtime > 0 ? (double)size * done / runtime / 1e6 : 0.) << endl;
+    fsC.close();
+    iblb_destroy(s);
+    if (rc) iblb::set_error(keep);
+    return rc;
+}

@@ -1,0 +1,158 @@
+// libiblb: x-slab coupling between GPUs (one solver per process).
+//
+// Each slab exports CUDA IPC handles of its two population buffers and of its step flags; after
+// iblb_connect the fused LB kernel of a boundary column stores its nine results a second time
+// straight into the neighbour's ghost columns through the peer mapping (NVLink / NVSwitch), and
+// steps are ordered by counters in peer-visible memory (slab_wait / slab_signal).  No staging
+// buffers, no host involvement per step, no collective.
+#include <unistd.h>
+
+#include <cstring>
+#include <string>
+
+#include "iblb_internal.h"
+
+using namespace iblb;
+
+static_assert(sizeof(cudaIpcMemHandle_t) <= IBLB_IPC_HANDLE_BYTES, "IPC handle size");
+
+extern "C" {
+
+int iblb_export_halo(iblb_solver *s, iblb_halo_handle *h) {
+    if (!s || !h) return IBLB_EINVAL;
+    IBLB_CUDA(cudaSetDevice(s->device));
+    memset(h, 0, sizeof *h);
+    cudaIpcMemHandle_t m;
+    for (int b = 0; b < 2; b++) {
+        IBLB_CUDA(cudaIpcGetMemHandle(&m, s->buf[b]));
+        memcpy(h->mem[b], &m, sizeof m);
+    }
+    IBLB_CUDA(cudaIpcGetMemHandle(&m, s->flags));
+    memcpy(h->flag, &m, sizeof m);
+    h->plane = (unsigned long long)s->L.plane;
+    h->ld = (unsigned)s->L.ld;
+    h->ghost = (unsigned)s->L.G;
+    h->width = (unsigned)s->L.W;
+    h->device = s->device;
+    h->pid = (int)getpid();
+    return IBLB_OK;
+}
+
+static int map_neighbour(iblb_solver *s, int face, const iblb_halo_handle *h) {
+    const bool self = (h->pid == (int)getpid() && h->device == s->device &&
+                       h->plane == (unsigned long long)s->L.plane && h->width == (unsigned)s->L.W);
+    // a handle exported by this very solver cannot be opened in its own process: use the pointers
+    cudaIpcMemHandle_t own;
+    bool is_own = false;
+    if (self) {
+        if (cudaIpcGetMemHandle(&own, s->buf[0]) == cudaSuccess)
+            is_own = memcmp(&own, h->mem[0], sizeof own) == 0;
+    }
+    if ((int)h->ghost != s->L.G || (int)h->ld != s->L.ld) {
+        set_error("iblb_connect: neighbour has a different ghost width or column pitch");
+        return IBLB_EINVAL;
+    }
+    for (int b = 0; b < 2; b++) {
+        double *base = nullptr;
+        if (is_own) {
+            base = s->buf[b];
+        } else {
+            cudaIpcMemHandle_t m;
+            memcpy(&m, h->mem[b], sizeof m);
+            void *ptr = nullptr;
+            IBLB_CUDA(cudaIpcOpenMemHandle(&ptr, m, cudaIpcMemLazyEnablePeerAccess));
+            s->nb_mapped[face][b] = ptr;
+            base = (double *)ptr;
+        }
+        s->nb[face][b] = Remote{base, (long long)h->plane, (int)h->ld, (int)h->ghost, (int)h->width};
+    }
+    int *flags = nullptr;
+    if (is_own) {
+        flags = s->flags;
+    } else {
+        cudaIpcMemHandle_t m;
+        memcpy(&m, h->flag, sizeof m);
+        void *ptr = nullptr;
+        IBLB_CUDA(cudaIpcOpenMemHandle(&ptr, m, cudaIpcMemLazyEnablePeerAccess));
+        s->nb_flag_mapped[face] = ptr;
+        flags = (int *)ptr;
+    }
+    // I am the RIGHT neighbour of my left neighbour: I write its flags[1]; and vice versa
+    s->nb_flag[face] = &flags[face == 0 ? 1 : 0];
+    if (face == 0) s->self_left = is_own;
+    else s->self_right = is_own;
+    return IBLB_OK;
+}
+
+int iblb_connect(iblb_solver *s, const iblb_halo_handle *left, const iblb_halo_handle *right) {
+    if (!s || !left || !right) return IBLB_EINVAL;
+    IBLB_CUDA(cudaSetDevice(s->device));
+    IBLB_CUDA(cudaStreamSynchronize(s->stream));
+    int rc = map_neighbour(s, 0, left);
+    if (rc) return rc;
+    rc = map_neighbour(s, 1, right);
+    if (rc) return rc;
+    s->connected = true;
+    if (s->graph_exec) {
+        cudaGraphExecDestroy(s->graph_exec);
+        s->graph_exec = nullptr;
+    }
+    // refresh the neighbours' ghost columns of the current source buffer with our boundary columns
+    dim3 g((s->L.YDIM + 255) / 256, s->L.G, 9);
+    halo_push<<<g, 256, 0, s->stream>>>(s->L, s->buf[s->cur], s->nb[0][s->cur], s->nb[1][s->cur]);
+    IBLB_CUDA(cudaGetLastError());
+    IBLB_CUDA(cudaStreamSynchronize(s->stream));
+    return IBLB_OK;
+}
+
+int iblb_connect_local(iblb_solver *s, iblb_solver *left, iblb_solver *right) {
+    if (!s || !left || !right) return IBLB_EINVAL;
+    IBLB_CUDA(cudaSetDevice(s->device));
+    IBLB_CUDA(cudaStreamSynchronize(s->stream));
+    iblb_solver *nbs[2] = {left, right};
+    for (int f = 0; f < 2; f++) {
+        iblb_solver *n = nbs[f];
+        if (n->L.G != s->L.G || n->L.ld != s->L.ld || n->L.YDIM != s->L.YDIM) {
+            set_error("iblb_connect_local: neighbour geometry differs");
+            return IBLB_EINVAL;
+        }
+        if (n->device != s->device) {
+            cudaError_t e = cudaDeviceEnablePeerAccess(n->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+                return cuda_fail(e, "cudaDeviceEnablePeerAccess");
+            cudaGetLastError();
+        }
+        for (int b = 0; b < 2; b++)
+            s->nb[f][b] = Remote{n->buf[b], n->L.plane, n->L.ld, n->L.G, n->L.W};
+        s->peer[f] = n;
+    }
+    s->self_left = (left == s);
+    s->self_right = (right == s);
+    s->connected = true;
+    if (!s->ev_boundary) IBLB_CUDA(cudaEventCreateWithFlags(&s->ev_boundary, cudaEventDisableTiming));
+    if (s->graph_exec) {
+        cudaGraphExecDestroy(s->graph_exec);
+        s->graph_exec = nullptr;
+    }
+    dim3 g((s->L.YDIM + 255) / 256, s->L.G, 9);
+    halo_push<<<g, 256, 0, s->stream>>>(s->L, s->buf[s->cur], s->nb[0][s->cur], s->nb[1][s->cur]);
+    IBLB_CUDA(cudaGetLastError());
+    IBLB_CUDA(cudaStreamSynchronize(s->stream));
+    return IBLB_OK;
+}
+
+int iblb_halo_ptrs(iblb_solver *s, int face, void **send, void **recv, size_t *bytes_per_pop,
+                   size_t *pop_stride_bytes) {
+    if (!s || face < 0 || face > 1) return IBLB_EINVAL;
+    const Lattice &L = s->L;
+    double *b = s->buf[s->cur];
+    // face 0: send our first G columns, receive into the left ghosts; face 1: last G columns /
+    // right ghosts.  Column blocks of G*ld doubles are contiguous within a population plane.
+    if (send) *send = b + L.off(face == 0 ? 0 : L.W - L.G, 0);
+    if (recv) *recv = b + L.off(face == 0 ? -L.G : L.W, 0);
+    if (bytes_per_pop) *bytes_per_pop = sizeof(double) * (size_t)L.G * L.ld;
+    if (pop_stride_bytes) *pop_stride_bytes = sizeof(double) * (size_t)L.plane;
+    return IBLB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,291 @@
+// libiblb: solver lifecycle and the time-step loop (replaces main.cu:389-587, 634-754, 817-934).
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "iblb_internal.h"
+
+namespace iblb {
+
+int cuda_fail(cudaError_t e, const char *what) {
+    set_error(std::string(what) + ": " + cudaGetErrorString(e));
+    cudaGetLastError();  // clear the sticky-free error state
+    return IBLB_ECUDA;
+}
+
+namespace {
+
+// which fine points can write marker j (main.cu:158-172 evaluated for every k in float, as the
+// kernel does); the winner of the write race is the lowest k (measured on B200) unless PICK_HIGHEST_K.
+void build_marker_table(std::vector<int> &k_of_j, bool lowest) {
+    k_of_j.assign(kMarkersPerCilium, -1);
+    for (int k = 0; k < kFinePoints; k++) {
+        const float arcl = 1. * k / kFinePoints;  // main.cu:100
+        const float s2 = 111 * arcl;              // main.cu:139
+        for (int j = 0; j < kMarkersPerCilium; j++) {
+            const float b_length = j;
+            if (fabsf(s2 - b_length) < 0.01) {
+                if (k_of_j[j] < 0 || !lowest) k_of_j[j] = k;
+            }
+        }
+    }
+}
+
+}  // namespace
+
+LbParams make_lb_params(const iblb_solver *s, int src_idx) {
+    LbParams q;
+    memset(&q, 0, sizeof q);
+    q.L = s->L;
+    q.src = s->buf[src_idx];
+    q.dst = s->buf[src_idx ^ 1];
+    q.left = s->nb[0][src_idx ^ 1];
+    q.right = s->nb[1][src_idx ^ 1];
+    q.band = s->band;
+    q.band_rows = s->band_rows;
+    q.band_ld = s->band_ld;
+    q.omega_plus = 1. / s->p.TAU;
+    q.omega_minus = 1. / s->p.TAU2;
+    q.kforce = 1. - 1. / (2. * s->p.TAU);
+    q.gx = s->p.gx;
+    q.gy = s->p.gy;
+    const bool half = s->p.c_num > 0 || (s->p.flags & IBLB_FLAG_HALF_FORCE_BODY);
+    q.half = half ? 0.5 : 0.0;
+    q.qacc = s->flux_on ? s->qacc : nullptr;
+    q.xq = s->flux_on ? s->xq_local : -1000;
+    q.col_begin = 0;
+    q.col_count = s->L.W;
+    q.split_at = 1 << 30;
+    q.split_skip = 0;
+    return q;
+}
+
+IbParams make_ib_params(const iblb_solver *s, int src_idx) {
+    IbParams q;
+    memset(&q, 0, sizeof q);
+    q.L = s->L;
+    q.src = s->buf[src_idx];
+    q.M = s->M;
+    q.coef = s->coef;
+    q.c_num = (int)s->p.c_num;
+    q.c_space = (int)s->p.c_space;
+    q.T = (int)s->p.T;
+    q.p_step = s->p.p_step;
+    q.it = (int)s->it;
+    q.it_ptr = nullptr;
+    q.Ns = s->Ns;
+    q.r_max = (int)(2 * kMarkersPerCilium / (double)s->p.c_space);  // main.cu:185
+    q.band = s->band;
+    q.band_rows = s->band_rows;
+    q.band_ld = s->band_ld;
+    return q;
+}
+
+}  // namespace iblb
+
+using namespace iblb;
+
+static int init_state(iblb_solver *s, const double *rho_dev, const double *u_dev) {
+    LbParams q = make_lb_params(s, 0);
+    q.dst = s->buf[0];
+    const long long n = (long long)s->L.W * s->L.YDIM;
+    lb_init<<<(unsigned)((n + 255) / 256), 256, 0, s->stream>>>(q, rho_dev, u_dev, s->p.u0_amp);
+    IBLB_CUDA(cudaGetLastError());
+    // ghost columns of buffer 0 (own opposite edge, or the connected neighbours)
+    dim3 g((s->L.YDIM + 255) / 256, s->L.G, 9);
+    halo_push<<<g, 256, 0, s->stream>>>(s->L, s->buf[0], s->nb[0][0], s->nb[1][0]);
+    IBLB_CUDA(cudaGetLastError());
+    if (s->band) IBLB_CUDA(cudaMemsetAsync(s->band, 0, sizeof(double) * 2 * s->L.W * s->band_ld, s->stream));
+    IBLB_CUDA(cudaMemsetAsync(s->qacc, 0, sizeof(double) * s->nq, s->stream));
+    if (s->it_dev) IBLB_CUDA(cudaMemsetAsync(s->it_dev, 0, sizeof(int), s->stream));
+    s->cur = 0;
+    s->it = 0;
+    IBLB_CUDA(cudaStreamSynchronize(s->stream));
+    return IBLB_OK;
+}
+
+extern "C" {
+
+int iblb_create(const iblb_params *pp, iblb_solver **out) {
+    if (!pp || !out) {
+        set_error("iblb_create: null argument");
+        return IBLB_EINVAL;
+    }
+    *out = nullptr;
+    const iblb_params &p = *pp;
+    if (p.XDIM < 4 || p.YDIM < 4 || (p.YDIM & 1)) {
+        set_error("iblb_create: XDIM, YDIM must be >= 4 and YDIM even");
+        return IBLB_EINVAL;
+    }
+    if (p.c_num > 0 && (p.XDIM != p.c_num * p.c_space || p.c_num > 2048 || p.YDIM < 128)) {
+        set_error("iblb_create: with cilia XDIM must equal c_num*c_space, c_num <= 2048, YDIM >= 128");
+        return IBLB_EINVAL;
+    }
+    if (!(p.TAU > 0.5) || !(p.TAU2 > 0.5)) {
+        set_error("iblb_create: relaxation times must exceed 1/2 (call iblb_params_derive)");
+        return IBLB_EINVAL;
+    }
+    const bool slab = p.slab_w != 0 && p.slab_w != p.XDIM;
+    if (slab && (p.slab_x0 + p.slab_w > p.XDIM)) {
+        set_error("iblb_create: slab exceeds the channel");
+        return IBLB_EINVAL;
+    }
+    if (p.device >= 0) IBLB_CUDA(cudaSetDevice(p.device));
+    iblb_solver *s = new iblb_solver();  // value-initialised: all members zero
+    s->p = p;
+    IBLB_CUDA(cudaGetDevice(&s->device));
+    Lattice &L = s->L;
+    L.XDIM = (int)p.XDIM;
+    L.YDIM = (int)p.YDIM;
+    L.W = slab ? (int)p.slab_w : (int)p.XDIM;
+    L.x0 = slab ? (int)p.slab_x0 : 0;
+    L.G = (slab && p.c_num > 0) ? 3 : 1;
+    L.ld = ((int)p.YDIM + 15) / 16 * 16;
+    L.plane = (long long)(L.W + 2 * L.G) * L.ld;
+    if (L.W < 2 * L.G + 2) {
+        delete s;
+        set_error("iblb_create: slab too narrow");
+        return IBLB_EINVAL;
+    }
+    s->vec2 = (p.YDIM % 64 == 0);
+    s->Ns = kMarkersPerCilium * (int)p.c_num;
+
+    int rc = IBLB_OK;
+#define TRY(call)                                   \
+    do {                                            \
+        cudaError_t e__ = (call);                   \
+        if (e__ != cudaSuccess && rc == IBLB_OK) rc = cuda_fail(e__, #call); \
+    } while (0)
+    const size_t pop_bytes = sizeof(double) * 9 * (size_t)L.plane;
+    TRY(cudaMalloc((void **)&s->buf[0], pop_bytes));
+    if (rc == IBLB_OK) TRY(cudaMalloc((void **)&s->buf[1], pop_bytes));
+    if (rc == IBLB_OK) TRY(cudaMemset(s->buf[0], 0, pop_bytes));
+    if (rc == IBLB_OK) TRY(cudaMemset(s->buf[1], 0, pop_bytes));
+    s->nq = s->vec2 ? (int)p.YDIM / 64 : 1;
+    TRY(cudaMalloc((void **)&s->qacc, sizeof(double) * s->nq));
+    if (!s->vec2) TRY(cudaMalloc((void **)&s->qpart, sizeof(double) * p.YDIM));
+    TRY(cudaMalloc((void **)&s->flags, 2 * sizeof(int)));
+    if (rc == IBLB_OK) TRY(cudaMemset(s->flags, 0, 2 * sizeof(int)));
+    TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    TRY(cudaEventCreate(&s->ev0));
+    TRY(cudaEventCreate(&s->ev1));
+    if (p.c_num > 0 && rc == IBLB_OK) {
+        s->band_rows = 128;
+        s->band_ld = 128;
+        TRY(cudaMalloc((void **)&s->band, sizeof(double) * 2 * (size_t)L.W * s->band_ld));
+        TRY(cudaMalloc((void **)&s->M.s, sizeof(float2) * s->Ns));
+        TRY(cudaMalloc((void **)&s->M.u_s, sizeof(float2) * s->Ns));
+        TRY(cudaMalloc((void **)&s->M.F_s, sizeof(float2) * s->Ns));
+        TRY(cudaMalloc((void **)&s->M.eps, sizeof(int) * s->Ns));
+        TRY(cudaMalloc((void **)&s->M.bbox, sizeof(float2) * p.c_num));
+        TRY(cudaMalloc((void **)&s->coef, sizeof(float) * kMarkersPerCilium * 28));
+        TRY(cudaMalloc((void **)&s->k_of_j_dev, sizeof(int) * kMarkersPerCilium));
+        TRY(cudaMalloc((void **)&s->it_dev, sizeof(int)));
+        if (rc == IBLB_OK) {
+            TRY(cudaMemset(s->M.s, 0, sizeof(float2) * s->Ns));
+            TRY(cudaMemset(s->M.u_s, 0, sizeof(float2) * s->Ns));
+            TRY(cudaMemset(s->M.F_s, 0, sizeof(float2) * s->Ns));
+            TRY(cudaMemset(s->M.eps, 0, sizeof(int) * s->Ns));
+            build_marker_table(s->k_of_j, (p.flags & IBLB_FLAG_PICK_HIGHEST_K) == 0);
+            TRY(cudaMemcpy(s->k_of_j_dev, s->k_of_j.data(), sizeof(int) * kMarkersPerCilium,
+                           cudaMemcpyHostToDevice));
+            ib_coef<<<1, 128, 0, s->stream>>>(s->k_of_j_dev, s->coef);
+            TRY(cudaGetLastError());
+        }
+    }
+#undef TRY
+    if (rc != IBLB_OK) {
+        std::string keep = iblb_last_error();
+        iblb_destroy(s);
+        set_error(keep);
+        return rc;
+    }
+    // flux plane x = XDIM-5 (ImmersedBoundary.cu:259); accumulated only where `spread` runs in
+    // the reference (cilia present) or the half-force extension asks for it
+    const int xq = (int)p.XDIM - 5 - L.x0;
+    s->xq_local = xq;
+    s->flux_on = (p.c_num > 0 || (p.flags & IBLB_FLAG_HALF_FORCE_BODY)) && xq >= 0 && xq < L.W;
+    // a lone solver is periodic with itself
+    for (int b = 0; b < 2; b++) {
+        Remote self{s->buf[b], L.plane, L.ld, L.G, L.W};
+        s->nb[0][b] = self;
+        s->nb[1][b] = self;
+    }
+    s->self_left = s->self_right = true;
+    s->nb_flag[0] = &s->flags[1];
+    s->nb_flag[1] = &s->flags[0];
+    rc = init_state(s, nullptr, nullptr);
+    if (rc != IBLB_OK) {
+        std::string keep = iblb_last_error();
+        iblb_destroy(s);
+        set_error(keep);
+        return rc;
+    }
+    *out = s;
+    return IBLB_OK;
+}
+
+int iblb_destroy(iblb_solver *s) {
+    if (!s) return IBLB_OK;
+    cudaSetDevice(s->device);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
+    for (int f = 0; f < 2; f++) {
+        for (int b = 0; b < 2; b++)
+            if (s->nb_mapped[f][b]) cudaIpcCloseMemHandle(s->nb_mapped[f][b]);
+        if (s->nb_flag_mapped[f]) cudaIpcCloseMemHandle(s->nb_flag_mapped[f]);
+    }
+    cudaFree(s->buf[0]); cudaFree(s->buf[1]); cudaFree(s->qacc); cudaFree(s->qpart);
+    cudaFree(s->flags); cudaFree(s->band); cudaFree(s->M.s); cudaFree(s->M.u_s);
+    cudaFree(s->M.F_s); cudaFree(s->M.eps); cudaFree(s->M.bbox); cudaFree(s->coef);
+    cudaFree(s->k_of_j_dev); cudaFree(s->it_dev);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->ev_boundary) cudaEventDestroy(s->ev_boundary);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    delete s;
+    return IBLB_OK;
+}
+
+int iblb_sync(iblb_solver *s) {
+    if (!s) return IBLB_EINVAL;
+    IBLB_CUDA(cudaStreamSynchronize(s->stream));
+    return IBLB_OK;
+}
+
+unsigned iblb_iteration(const iblb_solver *s) { return s ? s->it : 0; }
+
+int iblb_marker_fine_index(const iblb_solver *s, unsigned j) {
+    if (!s || j >= (unsigned)kMarkersPerCilium) return -1;
+    if (s->k_of_j.empty()) {
+        std::vector<int> t;
+        build_marker_table(t, (s->p.flags & IBLB_FLAG_PICK_HIGHEST_K) == 0);
+        return t[j];
+    }
+    return s->k_of_j[j];
+}
+
+int iblb_set_fields(iblb_solver *s, const double *rho, const double *u) {
+    if (!s || !rho || !u) {
+        set_error("iblb_set_fields: null argument");
+        return IBLB_EINVAL;
+    }
+    IBLB_CUDA(cudaSetDevice(s->device));
+    const size_t size = (size_t)s->L.W * s->L.YDIM;
+    double *d_rho = nullptr, *d_u = nullptr;
+    IBLB_CUDA(cudaMalloc((void **)&d_rho, sizeof(double) * size));
+    cudaError_t e = cudaMalloc((void **)&d_u, sizeof(double) * 2 * size);
+    if (e != cudaSuccess) {
+        cudaFree(d_rho);
+        return cuda_fail(e, "cudaMalloc");
+    }
+    cudaMemcpyAsync(d_rho, rho, sizeof(double) * size, cudaMemcpyHostToDevice, s->stream);
+    cudaMemcpyAsync(d_u, u, sizeof(double) * 2 * size, cudaMemcpyHostToDevice, s->stream);
+    int rc = init_state(s, d_rho, d_u);
+    cudaFree(d_rho);
+    cudaFree(d_u);
+    return rc;
+}
+
+}  // extern "C"

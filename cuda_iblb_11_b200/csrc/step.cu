@@ -1,0 +1,318 @@
+// libiblb: the time-step loop (replaces main.cu:817-934) and the state getters
+// (replace the D2H copies of main.cu:928, 944-982).
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "iblb_internal.h"
+
+namespace iblb {
+LbParams make_lb_params(const iblb_solver *s, int src_idx);
+IbParams make_ib_params(const iblb_solver *s, int src_idx);
+}  // namespace iblb
+using namespace iblb;
+
+namespace {
+
+struct PhaseEvents {
+    cudaEvent_t e[5];
+};
+
+// Launch the fused LB kernel over the column range encoded in q.
+int launch_lb(iblb_solver *s, const LbParams &q, cudaStream_t st, unsigned long long &launches) {
+    if (q.col_count <= 0) return IBLB_OK;
+    if (s->vec2) {
+        const long long n = (long long)q.col_count * (s->L.YDIM / 2);
+        lb_fused_v2<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(q);
+        launches += 1;
+    } else {
+        const long long n = (long long)q.col_count * s->L.YDIM;
+        lb_fused_v1<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(q, s->flux_on ? s->qpart : nullptr);
+        launches += 1;
+        const bool has_q = s->flux_on && s->xq_local >= 0;
+        if (has_q) {
+            // the flux column is covered by exactly one of the launches of a step
+            int c = s->xq_local;
+            bool covered;
+            if (q.split_skip)
+                covered = (c < q.split_at) || (c >= q.split_at + q.split_skip);
+            else
+                covered = c >= q.col_begin && c < q.col_begin + q.col_count;
+            if (covered) {
+                flux_reduce_v1<<<1, 256, 0, st>>>(s->qpart, s->L.YDIM, s->qacc);
+                launches += 1;
+            }
+        }
+    }
+    IBLB_CUDA(cudaGetLastError());
+    return IBLB_OK;
+}
+
+// One iteration: [slab wait] -> kinematics -> interpolate -> spread -> fused LB (boundary columns
+// first + signal, then interior, when coupled to other GPUs).
+int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEvents *pe,
+                      unsigned long long &launches) {
+    const int src = s->cur;
+    const bool coupled = s->connected && !(s->self_left && s->self_right);
+    const bool local = coupled && s->peer[0] != nullptr;
+    if (local) {
+        // same-process neighbours: their boundary kernels of the previous step (host lockstep)
+        for (int f = 0; f < 2; f++)
+            if (s->peer[f] != s && s->peer[f]->ev_boundary)
+                IBLB_CUDA(cudaStreamWaitEvent(st, s->peer[f]->ev_boundary, 0));
+    } else if (coupled) {
+        slab_wait<<<1, 32, 0, st>>>(&s->flags[0], &s->flags[1], (int)s->it);
+        launches += 1;
+    }
+    if (pe) cudaEventRecord(pe->e[0], st);
+    if (s->p.c_num > 0) {
+        IbParams ib = make_ib_params(s, src);
+        if (graph_mode) ib.it_ptr = s->it_dev;
+        ib_kinematics<<<ib.c_num, 128, 0, st>>>(ib);
+        if (pe) cudaEventRecord(pe->e[1], st);
+        ib_interpolate<<<(ib.Ns + 7) / 8, 256, 0, st>>>(ib);
+        if (pe) cudaEventRecord(pe->e[2], st);
+        dim3 g((s->L.W + kSpreadTileX - 1) / kSpreadTileX, s->band_rows / kSpreadTileY);
+        ib_spread<<<g, 256, 0, st>>>(ib);
+        launches += 3;
+        IBLB_CUDA(cudaGetLastError());
+    } else if (pe) {
+        cudaEventRecord(pe->e[1], st);
+        cudaEventRecord(pe->e[2], st);
+    }
+    if (pe) cudaEventRecord(pe->e[3], st);
+    LbParams q = make_lb_params(s, src);
+    if (coupled) {
+        const int G = s->L.G, W = s->L.W;
+        LbParams qb = q;  // boundary columns [0,G) and [W-G,W)
+        qb.col_begin = 0;
+        qb.col_count = 2 * G;
+        qb.split_at = G;
+        qb.split_skip = W - 2 * G;
+        int rc = launch_lb(s, qb, st, launches);
+        if (rc) return rc;
+        if (local) {
+            IBLB_CUDA(cudaEventRecord(s->ev_boundary, st));
+        } else {
+            slab_signal<<<1, 32, 0, st>>>(s->nb_flag[0], s->nb_flag[1], (int)s->it + 1);
+            launches += 1;
+        }
+        LbParams qi = q;  // interior: never touches a ghost column
+        qi.col_begin = G;
+        qi.col_count = W - 2 * G;
+        qi.left.G = 0;
+        qi.right.G = 0;
+        rc = launch_lb(s, qi, st, launches);
+        if (rc) return rc;
+    } else {
+        int rc = launch_lb(s, q, st, launches);
+        if (rc) return rc;
+    }
+    if (pe) cudaEventRecord(pe->e[4], st);
+    s->cur ^= 1;
+    s->it += 1;
+    return IBLB_OK;
+}
+
+int build_graph(iblb_solver *s) {
+    // two iterations (A->B, B->A); the iteration number is read from device memory
+    cudaGraph_t graph = nullptr;
+    const int cur0 = s->cur;
+    const unsigned it0 = s->it;
+    unsigned long long dummy = 0;
+    IBLB_CUDA(cudaStreamBeginCapture(s->stream, cudaStreamCaptureModeThreadLocal));
+    int rc = enqueue_iteration(s, s->stream, true, nullptr, dummy);
+    if (rc == IBLB_OK) rc = enqueue_iteration(s, s->stream, true, nullptr, dummy);
+    cudaError_t e = cudaStreamEndCapture(s->stream, &graph);
+    s->cur = cur0;
+    s->it = it0;
+    if (rc != IBLB_OK) {
+        if (graph) cudaGraphDestroy(graph);
+        return rc;
+    }
+    if (e != cudaSuccess) return cuda_fail(e, "cudaStreamEndCapture");
+    e = cudaGraphInstantiate(&s->graph_exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGraphInstantiate");
+    return IBLB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int iblb_step(iblb_solver *s, unsigned n_steps) {
+    if (!s) {
+        set_error("iblb_step: null solver");
+        return IBLB_EINVAL;
+    }
+    IBLB_CUDA(cudaSetDevice(s->device));
+    cudaStream_t st = s->stream;
+    unsigned long long launches = 0;
+    IBLB_CUDA(cudaEventRecord(s->ev0, st));
+    const bool coupled = s->connected && !(s->self_left && s->self_right);
+    // small grids are launch-bound: replay a captured two-iteration graph (needs cur == 0)
+    const long long nodes = (long long)s->L.W * s->L.YDIM;
+    const bool use_graph = !(s->p.flags & IBLB_FLAG_NO_GRAPH) && !coupled && nodes <= (1 << 22) &&
+                           n_steps >= 4;
+    unsigned left = n_steps;
+    if (use_graph) {
+        if (s->cur != 0) {
+            int rc = enqueue_iteration(s, st, false, nullptr, launches);
+            if (rc) return rc;
+            left--;
+        }
+        if (!s->graph_exec) {
+            int rc = build_graph(s);
+            if (rc) return rc;
+        }
+        if (s->it_dev)
+            IBLB_CUDA(cudaMemcpyAsync(s->it_dev, &s->it, sizeof(int), cudaMemcpyHostToDevice, st));
+        const unsigned per_iter = s->p.c_num > 0 ? 4u : 1u;
+        while (left >= 2) {
+            IBLB_CUDA(cudaGraphLaunch(s->graph_exec, st));
+            s->it += 2;
+            left -= 2;
+            launches += 2 * per_iter;
+        }
+    }
+    while (left > 0) {
+        int rc = enqueue_iteration(s, st, false, nullptr, launches);
+        if (rc) return rc;
+        left--;
+    }
+    IBLB_CUDA(cudaEventRecord(s->ev1, st));
+    s->timed = true;
+    s->last_launches = launches;
+    return IBLB_OK;
+}
+
+int iblb_last_step_seconds(iblb_solver *s, double *seconds) {
+    if (!s || !seconds || !s->timed) {
+        set_error("iblb_last_step_seconds: no timed step");
+        return IBLB_EINVAL;
+    }
+    IBLB_CUDA(cudaEventSynchronize(s->ev1));
+    float ms = 0.f;
+    IBLB_CUDA(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+    *seconds = 1e-3 * (double)ms;
+    return IBLB_OK;
+}
+
+int iblb_last_step_launches(iblb_solver *s, unsigned long long *n) {
+    if (!s || !n) return IBLB_EINVAL;
+    *n = s->last_launches;
+    return IBLB_OK;
+}
+
+int iblb_profile_phases(iblb_solver *s, unsigned reps, double *t_kin, double *t_interp,
+                        double *t_spread, double *t_lb) {
+    if (!s || reps == 0) return IBLB_EINVAL;
+    IBLB_CUDA(cudaSetDevice(s->device));
+    PhaseEvents pe;
+    for (auto &e : pe.e) IBLB_CUDA(cudaEventCreate(&e));
+    double acc[4] = {0, 0, 0, 0};
+    unsigned long long launches = 0;
+    int rc = IBLB_OK;
+    for (unsigned r = 0; r < reps && rc == IBLB_OK; r++) {
+        rc = enqueue_iteration(s, s->stream, false, &pe, launches);
+        if (rc) break;
+        cudaError_t e = cudaStreamSynchronize(s->stream);
+        if (e != cudaSuccess) {
+            rc = cuda_fail(e, "profile sync");
+            break;
+        }
+        for (int i = 0; i < 4; i++) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, pe.e[i], pe.e[i + 1]);
+            acc[i] += 1e-3 * ms;
+        }
+    }
+    for (auto &e : pe.e) cudaEventDestroy(e);
+    if (rc) return rc;
+    if (t_kin) *t_kin = acc[0] / reps;
+    if (t_interp) *t_interp = acc[1] / reps;
+    if (t_spread) *t_spread = acc[2] / reps;
+    if (t_lb) *t_lb = acc[3] / reps;
+    return IBLB_OK;
+}
+
+// ---- getters: recompute the macroscopic state of the last completed iteration from the buffer
+// that iteration pulled from (the step wrote the other one) ----
+static int run_moments(iblb_solver *s, double *rho, double *u, double *f, double *force) {
+    IBLB_CUDA(cudaSetDevice(s->device));
+    const size_t size = (size_t)s->L.W * s->L.YDIM;
+    const size_t n_out = (rho ? size : 0) + (u ? 2 * size : 0) + (f ? 9 * size : 0) +
+                         (force ? 2 * size : 0);
+    double *d = nullptr;
+    IBLB_CUDA(cudaMalloc((void **)&d, sizeof(double) * n_out));
+    double *d_rho = nullptr, *d_u = nullptr, *d_f = nullptr, *d_force = nullptr, *q = d;
+    if (rho) { d_rho = q; q += size; }
+    if (u) { d_u = q; q += 2 * size; }
+    if (f) { d_f = q; q += 9 * size; }
+    if (force) { d_force = q; q += 2 * size; }
+    const int streamed = s->it > 0;
+    LbParams lp = make_lb_params(s, streamed ? (s->cur ^ 1) : s->cur);
+    lb_moments<<<(unsigned)((size + 255) / 256), 256, 0, s->stream>>>(lp, streamed, d_rho, d_u, d_f,
+                                                                      d_force);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess && rho)
+        e = cudaMemcpyAsync(rho, d_rho, sizeof(double) * size, cudaMemcpyDeviceToHost, s->stream);
+    if (e == cudaSuccess && u)
+        e = cudaMemcpyAsync(u, d_u, sizeof(double) * 2 * size, cudaMemcpyDeviceToHost, s->stream);
+    if (e == cudaSuccess && f)
+        e = cudaMemcpyAsync(f, d_f, sizeof(double) * 9 * size, cudaMemcpyDeviceToHost, s->stream);
+    if (e == cudaSuccess && force)
+        e = cudaMemcpyAsync(force, d_force, sizeof(double) * 2 * size, cudaMemcpyDeviceToHost,
+                            s->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return cuda_fail(e, "iblb_get_*");
+    return IBLB_OK;
+}
+
+int iblb_get_fields(iblb_solver *s, double *rho, double *u) {
+    if (!s || (!rho && !u)) {
+        set_error("iblb_get_fields: null argument");
+        return IBLB_EINVAL;
+    }
+    return run_moments(s, rho, u, nullptr, nullptr);
+}
+
+int iblb_get_force(iblb_solver *s, double *force) {
+    if (!s || !force) return IBLB_EINVAL;
+    return run_moments(s, nullptr, nullptr, nullptr, force);
+}
+
+int iblb_get_populations(iblb_solver *s, double *f) {
+    if (!s || !f) return IBLB_EINVAL;
+    return run_moments(s, nullptr, nullptr, f, nullptr);
+}
+
+int iblb_get_markers(iblb_solver *s, float *pos, float *vel, float *force, int *eps) {
+    if (!s) return IBLB_EINVAL;
+    if (s->Ns == 0) return IBLB_OK;
+    IBLB_CUDA(cudaSetDevice(s->device));
+    IBLB_CUDA(cudaStreamSynchronize(s->stream));
+    const size_t nb = sizeof(float2) * s->Ns;
+    if (pos) IBLB_CUDA(cudaMemcpy(pos, s->M.s, nb, cudaMemcpyDeviceToHost));
+    if (vel) IBLB_CUDA(cudaMemcpy(vel, s->M.u_s, nb, cudaMemcpyDeviceToHost));
+    if (force) IBLB_CUDA(cudaMemcpy(force, s->M.F_s, nb, cudaMemcpyDeviceToHost));
+    if (eps) IBLB_CUDA(cudaMemcpy(eps, s->M.eps, sizeof(int) * s->Ns, cudaMemcpyDeviceToHost));
+    return IBLB_OK;
+}
+
+int iblb_get_flux(iblb_solver *s, double *Q) {
+    if (!s || !Q) return IBLB_EINVAL;
+    IBLB_CUDA(cudaSetDevice(s->device));
+    std::vector<double> part(s->nq);
+    IBLB_CUDA(cudaMemcpyAsync(part.data(), s->qacc, sizeof(double) * s->nq, cudaMemcpyDeviceToHost,
+                              s->stream));
+    IBLB_CUDA(cudaStreamSynchronize(s->stream));
+    double q = 0.;
+    for (int i = 0; i < s->nq; i++) q += part[i];  // fixed slot order
+    *Q = q;
+    return IBLB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,157 @@
+/* libiblb — C ABI of the B200-native IB-LBM time-step path.
+ *
+ * This is the drop-in boundary for the time-step loop of ptheywood/CUDA_IBLB_11
+ * (CUDA_IBLB_11/main.cu:817-934 and the eight kernels it launches: LatticeBoltzmann.cuh:4-10,
+ * ImmersedBoundary.cuh:4-8, main.cu:77, main.cu:176).  The reference has no plugin/FFI layer; its
+ * replaceable surface is main()'s argv (main.cu:284-296), the derived run parameters
+ * (main.cu:298-321,336), the device state main() copies back (main.cu:944-982) and the Data/
+ * files it writes (main.cu:589-631, 936-1005, 1030-1060).  Each entry point below names the
+ * reference lines it replaces.  Plain pointers and sizes only; every function returns 0 on
+ * success or an IBLB_E* code and never aborts (the reference prints and carries on,
+ * main.cu:724-728); iblb_last_error() gives the message.
+ *
+ * Host arrays use the REFERENCE's layouts (main.cu:469-501): node index j = y*XDIM + x;
+ * rho[size]; u/force plane-major [c*size + j]; populations AoS [9*j + i]; markers interleaved
+ * (x,y) floats [2*k + c].  The device layout (SoA, y-fastest, ghost columns) is internal.
+ */
+#ifndef IBLB_H
+#define IBLB_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IBLB_OK 0
+#define IBLB_EINVAL 1   /* bad argument / unsupported geometry */
+#define IBLB_ECUDA 2    /* a CUDA runtime call failed (message has cudaGetErrorString) */
+#define IBLB_EARGS 3    /* too few driver arguments (main.cu:284-289) */
+#define IBLB_ESIZE 4    /* XDIM < 2*LENGTH (main.cu:303-308) */
+#define IBLB_EIO 5      /* an output file could not be written */
+
+/* flags */
+#define IBLB_FLAG_HALF_FORCE_BODY 1u /* Guo half-force velocity also for the uniform body force
+                                        when no cilia are present (extension; the reference's LB
+                                        chain alone applies none, LatticeBoltzmann.cu:404-405) */
+#define IBLB_FLAG_PICK_HIGHEST_K 2u  /* resolve the define_filament marker write race
+                                        (main.cu:158-172) for the HIGHER fine-point index, i.e.
+                                        sequential semantics.  Default: the lower index, which is
+                                        what the reference's CUDA build does on a B200 (measured:
+                                        95 of 96 markers per cilium; marker 32's two candidates
+                                        sit in different warps and its winner varies per step) */
+#define IBLB_FLAG_NO_GRAPH 4u        /* launch kernels directly instead of CUDA-graph batches */
+
+typedef struct iblb_params {
+    /* --- the ten driver arguments, main.cu:291-296 --- */
+    unsigned c_fraction, c_num, c_space;
+    double Re;
+    float T_num;
+    unsigned T_pow;
+    float I_pow;
+    unsigned P_num;
+    int ShARC, BigData;
+    /* --- derived, main.cu:298-321,336 (filled by iblb_params_derive) --- */
+    unsigned XDIM, YDIM, T, ITERATIONS, INTERVAL, LENGTH;
+    int p_step;
+    double SPEED, t_scale, x_scale, s_scale, TAU, TAU2, Ma;
+    /* --- extensions (all 0 in a reference run) --- */
+    double gx, gy;     /* uniform body force (config C2) */
+    double u0_amp;     /* initial u_x(y) = u0_amp*sin(2*pi*(y+0.5)/YDIM) */
+    unsigned flags;    /* IBLB_FLAG_* */
+    int device;        /* CUDA device ordinal; -1 = current device */
+    /* x-slab of a wider periodic channel (multi-GPU): this solver owns global columns
+     * [slab_x0, slab_x0+slab_w); slab_w == 0 means the whole channel (single GPU). */
+    unsigned slab_x0, slab_w;
+} iblb_params;
+
+typedef struct iblb_solver iblb_solver;
+
+/* ---- driver surface ---------------------------------------------------------------------- */
+
+/* Defaults of main.cu:267-282 (c_fraction 1, c_num 6, c_space 48, Re 1, T_num 1, T_pow 1 ...). */
+void iblb_params_default(iblb_params *p);
+/* argv -> the ten arguments, exactly as main.cu:284-296 parses them (one stream, same types).
+ * Also accepts the scripts' legacy 8-value line `c_fraction c_num Re T ITERATIONS P_num ShARC
+ * BigData` (app.sh:7, cilia6.sh:7-17) and maps it to the 10-value form with c_space = 48.
+ * Returns IBLB_EARGS with the reference's message in iblb_last_error() when too few are given.
+ * Calls iblb_params_derive on success. */
+int iblb_params_from_args(int argc, const char *const *argv, iblb_params *p);
+/* main.cu:298-321,336: XDIM, T, ITERATIONS, INTERVAL, scales, TAU, TAU2, Ma, p_step.  YDIM and
+ * LENGTH keep their values when non-zero (reference: 192 and 96, main.cu:271,279).
+ * Returns IBLB_ESIZE when XDIM < 2*LENGTH with cilia present (main.cu:303-308). */
+int iblb_params_derive(iblb_params *p);
+
+/* ---- lifecycle (replaces main.cu:389-587 allocation, 634-754 initial state) ------------- */
+int iblb_create(const iblb_params *p, iblb_solver **out);
+int iblb_destroy(iblb_solver *s);
+/* Advance n_steps iterations of the loop main.cu:817-934.  Asynchronous on the solver's stream;
+ * every getter synchronises. */
+int iblb_step(iblb_solver *s, unsigned n_steps);
+int iblb_sync(iblb_solver *s);
+unsigned iblb_iteration(const iblb_solver *s);
+
+/* ---- state access (replaces the D2H copies of main.cu:928, 944-982) ---------------------- */
+/* rho[size], u[2*size] of the last completed iteration, reference layout; either may be NULL.
+ * For a slab solver, size = slab_w*YDIM and x is slab-local. */
+int iblb_get_fields(iblb_solver *s, double *rho, double *u);
+int iblb_get_force(iblb_solver *s, double *force /*2*size*/);
+/* post-streaming populations f[9*size] of the last completed iteration (what d_f holds after
+ * `streaming`, LatticeBoltzmann.cu:173-373) */
+int iblb_get_populations(iblb_solver *s, double *f);
+int iblb_get_markers(iblb_solver *s, float *pos, float *vel, float *force /*2*Ns each*/,
+                     int *eps /*Ns*/);
+/* cumulative flux Q of main.cu:928 / ImmersedBoundary.cu:259-264 */
+int iblb_get_flux(iblb_solver *s, double *Q);
+/* Replace the state by the equilibrium of (rho,u) as main.cu:722-754 does for rho=1,u=0;
+ * resets the iteration counter and Q.  Host arrays, reference layout. */
+int iblb_set_fields(iblb_solver *s, const double *rho, const double *u);
+/* which fine point k in [0,9600) feeds marker j in [0,96) (main.cu:158-172) */
+int iblb_marker_fine_index(const iblb_solver *s, unsigned j);
+
+/* ---- measurement helpers ------------------------------------------------------------------ */
+/* Device time (CUDA events on the solver's stream) of the last iblb_step call, seconds. */
+int iblb_last_step_seconds(iblb_solver *s, double *seconds);
+/* Kernel launches issued by the last iblb_step call (graph nodes count one each). */
+int iblb_last_step_launches(iblb_solver *s, unsigned long long *n);
+/* Time the phases of one iteration separately (kinematics, interpolate, spread, fused LB),
+ * averaged over `reps` iterations that DO advance the state; seconds per phase. */
+int iblb_profile_phases(iblb_solver *s, unsigned reps, double *t_kin, double *t_interp,
+                        double *t_spread, double *t_lb);
+
+/* ---- x-slab coupling (multi-GPU; one solver per process/GPU) ----------------------------- */
+#define IBLB_IPC_HANDLE_BYTES 64
+typedef struct iblb_halo_handle {
+    unsigned char mem[2][IBLB_IPC_HANDLE_BYTES]; /* cudaIpcMemHandle_t of population buffers A,B */
+    unsigned char flag[IBLB_IPC_HANDLE_BYTES];   /* cudaIpcMemHandle_t of the step flags */
+    unsigned long long plane;  /* doubles per population plane */
+    unsigned ld, ghost, width; /* column pitch (doubles), ghost columns, owned columns */
+    int device, pid;
+} iblb_halo_handle;
+/* Export this slab's buffers; import the left/right neighbours' (periodic ring).  After
+ * iblb_connect the fused LB kernel stores its outgoing boundary columns straight into the
+ * neighbours' ghost columns over NVLink and steps are ordered by device-side flags. */
+int iblb_export_halo(iblb_solver *s, iblb_halo_handle *h);
+int iblb_connect(iblb_solver *s, const iblb_halo_handle *left, const iblb_halo_handle *right);
+/* Same-process variant (several solvers driven by one host thread, on one or several GPUs):
+ * neighbours are given as solver handles, ordering uses CUDA events instead of flags.  The caller
+ * must advance all slabs in lockstep: iblb_step(slab, 1) for every slab, then the next step. */
+int iblb_connect_local(iblb_solver *s, iblb_solver *left, iblb_solver *right);
+/* Staged alternative (NCCL / host transports): device pointers of the contiguous send and
+ * receive column blocks for face 0 (left) / 1 (right) of the CURRENT source buffer. */
+int iblb_halo_ptrs(iblb_solver *s, int face, void **send, void **recv, size_t *bytes_per_pop,
+                   size_t *pop_stride_bytes);
+/* In staged mode iblb_step(1) must be followed by an exchange before the next step. */
+
+/* ---- driver-level run (replaces main() as a whole: SimLog, flux, fluid/cilia files) ------ */
+/* Runs ITERATIONS steps writing the reference's Data/ tree under `root` (NULL: "Data/").
+ * main.cu:589-631, 758-790, 936-1005, 1030-1060. */
+int iblb_run(const iblb_params *p, const char *root);
+
+const char *iblb_last_error(void);
+const char *iblb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
