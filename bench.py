@@ -1,0 +1,387 @@
+#!/usr/bin/env python
+"""bench.py — MLUPS of the IB-LBM time-step path on B200 (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c4|c1|c3] [--impl reference]
+
+N = 1 : configs[1] of BASELINE.json — pure-LB channel 8192x8192, uniform body force, FP64.
+N > 1 : launched by torch.distributed.run, one rank per GPU.  The channel is N*8192 wide and 8192
+        high, x-slab partitioned (8192 columns per GPU, weak scaling); boundary columns are stored
+        straight into the neighbours' ghost columns over NVLink by the fused kernel (CUDA IPC peer
+        mappings), steps ordered by device-side flags; torch.distributed only exchanges the IPC
+        handles and provides the barrier / max-over-ranks.
+A "step" is one lattice update of the whole channel.  value = nodes * K / (max over ranks of the
+device time of the K timed steps, CUDA events on the solver's stream) / 1e6.
+`--impl reference` runs the reference's own kernels (nvcc sm_100a build of the unmodified sources,
+oracle/_ref/libiblb_ref_cuda.so — the reference has no CPU path) on the same configuration.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BYTES_PER_LUP = 144  # 9 populations x 8 B x (1 read + 1 write), SURVEY.md §8(d)
+
+WORKLOADS = {
+    # name: (XDIM per GPU or total, YDIM, c_num total or per gpu, c_space, scaling)
+    "c2": dict(desc="pure-LB channel 8192x8192 per GPU, body force gx=1e-7, no IB (configs[1])",
+               X=8192, Y=8192, c_num=0, c_space=48, scaling="weak", gx=1e-7),
+    "c4": dict(desc="32768x32768 channel, 256-cilia carpet, slab-partitioned (configs[3])",
+               X=32768, Y=32768, c_num=256, c_space=128, scaling="strong", gx=0.0),
+    "c1": dict(desc="cilia6.sh case 288x192, 6 cilia (configs[0])",
+               X=288, Y=192, c_num=6, c_space=48, scaling="replicas", gx=0.0),
+    "c3": dict(desc="cilia12.sh case 576x192, 12 cilia (configs[2])",
+               X=576, Y=192, c_num=12, c_space=48, scaling="replicas", gx=0.0),
+}
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic():
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture, or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+            return json.load(f)
+    except Exception:
+        return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100", "-i", str(self.gpu)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = [l for (t, l) in self.lines if t0 - 0.05 <= t <= t1 + 0.15] or \
+               [l for (_, l) in self.lines]
+        for l in rows:
+            c = [x.strip() for x in l.split(",")]
+            try:
+                sm.append(float(c[1]))
+                mx = float(c[2])
+                for n, v in zip(names, c[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return world, rank, local
+
+
+class Plumbing:
+    """torch.distributed (NCCL) for barrier / max / handle exchange; a no-op at world size 1."""
+
+    def __init__(self, n_gpus):
+        self.world, self.rank, self.local = dist_env()
+        self.dist = None
+        self.torch = None
+        if self.world > 1:
+            import torch
+            import torch.distributed as dist
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            torch.cuda.set_device(self.local)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            self.dist, self.torch = dist, torch
+
+    def barrier(self):
+        if self.dist:
+            self.dist.barrier()
+
+    def max(self, v):
+        if not self.dist:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum(self, v):
+        if not self.dist:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def all_gather_bytes(self, b):
+        if not self.dist:
+            return [b]
+        out = [None] * self.world
+        self.dist.all_gather_object(out, b)
+        return out
+
+    def close(self):
+        if self.dist:
+            self.dist.barrier()
+            self.dist.destroy_process_group()
+
+
+def pinned(n):
+    """float64 host buffer in pinned memory (torch is the allocator; plumbing only)."""
+    try:
+        import torch
+        return torch.empty(n, dtype=torch.float64, pin_memory=True).numpy()
+    except Exception:
+        return np.empty(n)
+
+
+def make_solver(pl, wl, n_gpus):
+    import ctypes
+    from cuda_iblb_11_b200 import HaloHandle, Params, Solver
+    w = WORKLOADS[wl]
+    if w["scaling"] == "weak":
+        X_total, Wl = w["X"] * n_gpus, w["X"]
+    elif w["scaling"] == "strong":
+        X_total, Wl = w["X"], w["X"] // n_gpus
+    else:  # replicas: every rank runs the whole (small) case
+        X_total, Wl = w["X"], w["X"]
+    slabbed = n_gpus > 1 and w["scaling"] != "replicas"
+    p = Params.channel(X_total, w["Y"], c_num=w["c_num"], c_space=w["c_space"], gx=w["gx"],
+                       device=pl.local, slab_x0=pl.rank * Wl if slabbed else 0,
+                       slab_w=Wl if slabbed else 0)
+    s = Solver(p)
+    if slabbed:
+        mine = bytes(s.export_halo())
+        hs = [HaloHandle.from_buffer_copy(b) for b in pl.all_gather_bytes(mine)]
+        s.connect(hs[(pl.rank - 1) % n_gpus], hs[(pl.rank + 1) % n_gpus])
+        pl.barrier()
+    nodes_total = X_total * w["Y"] * (n_gpus if w["scaling"] == "replicas" else 1)
+    return s, p, nodes_total, Wl * w["Y"]
+
+
+def run_ours(a):
+    pl = Plumbing(a.gpus)
+    n = max(1, a.gpus)
+    s, p, nodes_total, nodes_local = make_solver(pl, a.workload, n)
+    s.step(a.warmup)
+    s.sync()
+    pl.barrier()
+    sampler = ClockSampler(pl.local)
+    if pl.rank == 0:
+        sampler.start()
+        time.sleep(0.25)
+    # ---- timed region: K steps, device time by CUDA events on the solver's stream ----
+    pl.barrier()
+    s.sync()
+    t0 = time.time()
+    s.step(a.steps)
+    s.sync()
+    t_dev = s.last_step_seconds
+    launches = s.last_step_launches
+    pl.barrier()
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1) if pl.rank == 0 else None
+    t = pl.max(t_dev)
+    launches_total = int(pl.sum(float(launches)))
+    value = nodes_total * a.steps / t / 1e6
+
+    # ---- e2e: same metric through the C ABI with HOST buffers: upload (rho,u), K steps with the
+    # reference's per-step flux readback (main.cu:928), download (rho,u) (main.cu:944-952) ----
+    rho = pinned(nodes_local)
+    u = pinned(2 * nodes_local)
+    rho[:] = 1.0
+    u[:] = 0.0
+    pl.barrier()
+    s.sync()
+    e0 = time.perf_counter()
+    s.set_fields(rho, u)
+    pl.barrier()  # every slab re-initialised before any neighbour pulls from its ghosts
+    q = 0.0
+    for _ in range(a.steps):
+        s.step(1)
+        q = s.Q
+    s.fields(rho, u)
+    pl.barrier()
+    e1 = pl.max(time.perf_counter() - e0)
+    e2e_value = nodes_total * a.steps / e1 / 1e6
+    h2d = 24 * nodes_local * n / a.steps
+    d2h = (24 * nodes_local * n + 8 * max(1, p.YDIM // 64) * n * a.steps) / a.steps
+
+    peak, peak_src = measured_peak()
+    # dominant kernel = lb_fused_v2: in the pure-LB workload the timed region is K launches of it
+    lb_launches_per_rank = a.steps * (1 if n == 1 or WORKLOADS[a.workload]["scaling"] == "replicas" else 2)
+    achieved = BYTES_PER_LUP * (nodes_total / n) * a.steps / t_dev / 1e9
+    tr = ncu_traffic()
+    roof = {"bound": "hbm", "kernel": "lb_fused_v2", "achieved": round(achieved, 1),
+            "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+            "frac": round(achieved / peak, 4),
+            "algorithmic_bytes_per_launch": BYTES_PER_LUP * nodes_local,
+            "avg_launch_ms": round(1e3 * t_dev / a.steps, 4),
+            "launches_of_kernel": lb_launches_per_rank,
+            "traffic": tr.get("dram_bytes_per_launch") if tr else None}
+    out = None
+    if pl.rank == 0:
+        out = {
+            "metric": "MLUPS", "value": round(value, 1), "unit": "MLUPS", "n_gpus": n,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(1e3 * t / a.steps, 4),
+            "higher_is_better": True, "scaling": WORKLOADS[a.workload]["scaling"],
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "%s: %s" % (a.workload, WORKLOADS[a.workload]["desc"]),
+                       "grid": [int(p.XDIM), int(p.YDIM)], "columns_per_gpu": nodes_local // int(p.YDIM),
+                       "parallelism": "x-slabs x%d, NVLink peer-store halos" % n if n > 1 else "1 GPU",
+                       "l2_policy": "working set %.1f GB per GPU >> 126 MB L2" % (nodes_local * 144 / 1e9)
+                       if nodes_local * 144 > 1e9 else "L2-resident (latency-bound case)"},
+            "gpu_launches": launches_total,
+            "e2e": {"value": round(e2e_value, 1), "unit": "MLUPS",
+                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "what": "iblb_set_fields(host rho,u) + K x [iblb_step(1) + iblb_get_flux] + "
+                            "iblb_get_fields(host), wall clock, max over ranks"},
+            "roofline": roof, "clocks": clocks, "flux_check": q,
+        }
+    s.close()
+    return pl, out
+
+
+def cpu_baseline(a, target_seconds=12.0):
+    """Oracle port (plain C + OpenMP, all host cores) on a bounded sample of the same workload:
+    a narrower channel of the same height; MLUPS is per-node so the figure carries over."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from checkers import Checker, make_params
+    w = WORKLOADS[a.workload]
+    cores = os.cpu_count() or 1
+    if w["c_num"] == 0:
+        X, Y, c_num = 256, w["Y"], 0
+    else:
+        X, Y, c_num = 48 * 6, 192, 6
+    c = Checker("oracle", make_params(X, Y, c_num=c_num, gx=w["gx"], threads=cores))
+    c.step(1)
+    c.step(2)
+    per = max(c.last_step_seconds / 2, 1e-6)
+    n = int(max(2, min(2000, target_seconds / per)))
+    c.step(n)
+    t = c.last_step_seconds
+    c.close()
+    return {"value": round(X * Y * n / t / 1e6, 2), "unit": "MLUPS", "cores": cores,
+            "kind": "port",
+            "sample": "oracle port (C+OpenMP), %dx%d%s, %d steps, %.1f s" % (
+                X, Y, " with %d cilia" % c_num if c_num else " pure LB", n, t)}
+
+
+def run_reference(a):
+    """Reference arm: the reference's own kernels.  The reference has no CPU path (BASELINE.json),
+    so this is its CUDA build for sm_100a (oracle/_ref/libiblb_ref_cuda.so, unmodified sources)
+    on one B200; if that library is absent, the same kernels compiled as host C++
+    (libiblb_ref_cpu.so) or the oracle port on a bounded sample."""
+    world, rank, local = dist_env()
+    if rank != 0:
+        return None
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from checkers import Checker, available, make_params
+    w = WORKLOADS[a.workload]
+    cores = os.cpu_count() or 1
+    X, Y, c_num = w["X"], w["Y"], w["c_num"]
+    kind, sample = "ref_cuda", None
+    if w["scaling"] == "strong" or not available("ref_cuda"):
+        # the reference cannot address 32768^2 (32-bit 9*j index, 352 GB): largest comparable grid
+        if available("ref_cuda"):
+            X, Y, c_num = 8192, 192, 64
+            sample = "reference CUDA build on 8192x192 with 64 cilia (cannot address 32768^2)"
+        else:
+            kind = "ref_cpu" if available("ref_cpu") else "oracle"
+            X, Y, c_num = (256, w["Y"], 0) if w["c_num"] == 0 else (288, 192, 6)
+            sample = "%s on %dx%d (no GPU build of the reference available)" % (kind, X, Y)
+    c = Checker(kind, make_params(X, Y, c_num=c_num, c_space=w["c_space"] if c_num else 48,
+                                  gx=w["gx"], threads=cores))
+    steps, warm = a.steps, a.warmup
+    if kind != "ref_cuda":
+        steps, warm = min(steps, 3), 1
+    c.step(warm)
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.25)
+    t0 = time.time()
+    c.step(steps)
+    t = c.last_step_seconds
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1)
+    c.close()
+    value = X * Y * steps / t / 1e6
+    launches = steps * (4 + (4 if c_num else 0)) if kind == "ref_cuda" else 0
+    if sample is None:
+        sample = "reference CUDA build (nvcc sm_100a, unmodified sources) on the full %dx%d" % (X, Y)
+    return {
+        "impl": "reference", "metric": "MLUPS", "value": round(value, 2), "unit": "MLUPS",
+        "n_gpus": 1, "steps": steps, "warmup": warm, "ms_per_step": round(1e3 * t / steps, 4),
+        "higher_is_better": True, "scaling": w["scaling"], "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": "%s: %s" % (a.workload, w["desc"]), "grid": [X, Y]},
+        "gpu_launches": launches,
+        "cpu_baseline": {"value": round(value, 2), "unit": "MLUPS", "cores": cores,
+                         "kind": "reference", "sample": sample + "; the reference has no CPU path"},
+        "e2e": {"value": round(value, 2), "unit": "MLUPS", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "clocks": clocks,
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    a = ap.parse_args()
+    a.warmup = max(a.warmup, 3)
+    if a.impl == "reference":
+        out = run_reference(a)
+        if out is not None:
+            print(json.dumps(out), flush=True)
+        return 0
+    pl, out = run_ours(a)
+    if out is not None:
+        if max(1, a.gpus) == 1 and not a.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline(a)
+        print(json.dumps(out), flush=True)
+    pl.close()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

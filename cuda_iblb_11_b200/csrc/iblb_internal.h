@@ -71,6 +71,7 @@ struct iblb_solver {
     int *nb_flag[2];           // left neighbour's flags[1], right neighbour's flags[0]
     void *nb_flag_mapped[2];
     bool self_left, self_right;
+    int flag_base;             // step flags carry flag_base + it (monotonic across set_fields)
     iblb_solver *peer[2];      // same-process neighbours (iblb_connect_local)
     cudaEvent_t ev_boundary;   // recorded after this slab's boundary-column kernel
 };

@@ -100,6 +100,7 @@ static int init_state(iblb_solver *s, const double *rho_dev, const double *u_dev
     IBLB_CUDA(cudaMemsetAsync(s->qacc, 0, sizeof(double) * s->nq, s->stream));
     if (s->it_dev) IBLB_CUDA(cudaMemsetAsync(s->it_dev, 0, sizeof(int), s->stream));
     s->cur = 0;
+    s->flag_base += (int)s->it;  // all slabs reset together: later flag values stay above old ones
     s->it = 0;
     IBLB_CUDA(cudaStreamSynchronize(s->stream));
     return IBLB_OK;

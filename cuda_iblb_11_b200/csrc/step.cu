@@ -61,7 +61,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
             if (s->peer[f] != s && s->peer[f]->ev_boundary)
                 IBLB_CUDA(cudaStreamWaitEvent(st, s->peer[f]->ev_boundary, 0));
     } else if (coupled) {
-        slab_wait<<<1, 32, 0, st>>>(&s->flags[0], &s->flags[1], (int)s->it);
+        slab_wait<<<1, 32, 0, st>>>(&s->flags[0], &s->flags[1], s->flag_base + (int)s->it);
         launches += 1;
     }
     if (pe) cudaEventRecord(pe->e[0], st);
@@ -94,7 +94,8 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         if (local) {
             IBLB_CUDA(cudaEventRecord(s->ev_boundary, st));
         } else {
-            slab_signal<<<1, 32, 0, st>>>(s->nb_flag[0], s->nb_flag[1], (int)s->it + 1);
+            slab_signal<<<1, 32, 0, st>>>(s->nb_flag[0], s->nb_flag[1],
+                                        s->flag_base + (int)s->it + 1);
             launches += 1;
         }
         LbParams qi = q;  // interior: never touches a ghost column

@@ -71,6 +71,10 @@ typedef struct Oracle {
     double Q;
     double last_seconds;
     int threads;
+    /* optional replay of the reference's timing-dependent race on marker 32 (its two candidate
+     * fine points sit in different warps): trace[it*c_num+m] != 0 -> higher k wins */
+    unsigned char *trace;
+    int trace_steps;
 } Oracle;
 
 /* ------------------------------------------------------------------ LB */
@@ -366,7 +370,10 @@ static void o_define_filament(Oracle *o, int it) {
             lasts[0] = s[0]; /* :154-155 */
             lasts[1] = s[1];
             const int j = m * LENGTH + o->cand_j[q]; /* :158-172 */
-            if (lowest && written[o->cand_j[q]]) continue;
+            int keep_first = lowest;
+            if (o->trace && it < o->trace_steps && o->cand_j[q] == 32)
+                keep_first = !o->trace[(size_t)it * o->p.c_num + m];
+            if (keep_first && written[o->cand_j[q]]) continue;
             written[o->cand_j[q]] = 1;
             o->b_points[5 * j + 0] = s[0];
             o->b_points[5 * j + 1] = s[1];
@@ -522,8 +529,21 @@ int oracle_marker_fine_index(void *h, int j) {
     return best;
 }
 
+void oracle_set_marker32_trace(void *h, const unsigned char *trace, int n_steps) {
+    Oracle *o = (Oracle *)h;
+    free(o->trace);
+    o->trace = NULL;
+    o->trace_steps = 0;
+    if (trace && n_steps > 0) {
+        o->trace = (unsigned char *)malloc((size_t)n_steps * o->p.c_num);
+        memcpy(o->trace, trace, (size_t)n_steps * o->p.c_num);
+        o->trace_steps = n_steps;
+    }
+}
+
 void oracle_destroy(void *h) {
     Oracle *o = (Oracle *)h;
+    free(o->trace);
     free(o->u); free(o->rho); free(o->f0); free(o->f); free(o->f1); free(o->F); free(o->force);
     free(o->s); free(o->u_s); free(o->F_s); free(o->b_points); free(o->epsilon);
     free(o->cand_k); free(o->cand_j); free(o->fine); free(o->lasts);

@@ -20,6 +20,8 @@ void oracle_destroy(void *h);
 double oracle_last_step_seconds(void *h);
 const char *oracle_kind(void);
 int oracle_marker_fine_index(void *h, int j);
+/* replay which candidate won the reference's race on marker 32, per step and cilium */
+void oracle_set_marker32_trace(void *h, const unsigned char *trace, int n_steps);
 
 /* derived run parameters of main.cu:291-321,336 */
 typedef struct oracle_derived {

@@ -98,6 +98,12 @@ class Checker:
         self.size = params.XDIM * params.YDIM
         self.Ns = 96 * params.c_num
 
+    def set_marker32_trace(self, trace):
+        """oracle port only: trace[it, m] != 0 -> the higher fine point wins marker 32 at step it."""
+        t = np.ascontiguousarray(trace, np.uint8)
+        self.lib.oracle_set_marker32_trace.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+        self.lib.oracle_set_marker32_trace(self.h, t.ctypes.data, t.shape[0])
+
     def step(self, n=1):
         rc = self._step(self.h, n)
         if rc != 0:
