@@ -75,6 +75,11 @@ typedef struct Oracle {
      * fine points sit in different warps): trace[it*c_num+m] != 0 -> higher k wins */
     unsigned char *trace;
     int trace_steps;
+    /* optional replay of marker 32 exactly as the reference produced it (covers torn writes of the
+     * racing stores as well): replay[(it*c_num+m)*4 + {0,1,2,3}] = s_x, s_y, u_s_x, u_s_y after
+     * boundary_check's translation (main.cu:193-209) */
+    float *replay;
+    int replay_steps;
 } Oracle;
 
 /* ------------------------------------------------------------------ LB */
@@ -403,6 +408,16 @@ static void o_boundary_check(Oracle *o, int it) {
         }
         o->epsilon[j] = 1;
     }
+    if (o->replay && it < o->replay_steps) {
+        for (int m = 0; m < c_num; m++) {
+            const float *r = o->replay + 4 * ((size_t)it * c_num + m);
+            const int j = m * LENGTH + 32;
+            o->s[2 * j + 0] = r[0];
+            o->s[2 * j + 1] = r[1];
+            o->u_s[2 * j + 0] = r[2];
+            o->u_s[2 * j + 1] = r[3];
+        }
+    }
     for (int j = 0; j < o->Ns; j++) { /* :217-248 */
         const int m = (j - j % LENGTH) / LENGTH;
         const float x_m = o->s[2 * j + 0], y_m = o->s[2 * j + 1];
@@ -541,9 +556,23 @@ void oracle_set_marker32_trace(void *h, const unsigned char *trace, int n_steps)
     }
 }
 
+void oracle_set_marker32_replay(void *h, const float *vals, int n_steps) {
+    Oracle *o = (Oracle *)h;
+    free(o->replay);
+    o->replay = NULL;
+    o->replay_steps = 0;
+    if (vals && n_steps > 0) {
+        const size_t n = (size_t)n_steps * o->p.c_num * 4;
+        o->replay = (float *)malloc(sizeof(float) * n);
+        memcpy(o->replay, vals, sizeof(float) * n);
+        o->replay_steps = n_steps;
+    }
+}
+
 void oracle_destroy(void *h) {
     Oracle *o = (Oracle *)h;
     free(o->trace);
+    free(o->replay);
     free(o->u); free(o->rho); free(o->f0); free(o->f); free(o->f1); free(o->F); free(o->force);
     free(o->s); free(o->u_s); free(o->F_s); free(o->b_points); free(o->epsilon);
     free(o->cand_k); free(o->cand_j); free(o->fine); free(o->lasts);

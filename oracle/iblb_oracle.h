@@ -22,6 +22,9 @@ const char *oracle_kind(void);
 int oracle_marker_fine_index(void *h, int j);
 /* replay which candidate won the reference's race on marker 32, per step and cilium */
 void oracle_set_marker32_trace(void *h, const unsigned char *trace, int n_steps);
+/* replay marker 32 of every cilium as recorded from the reference's CUDA build:
+ * vals[(it*c_num+m)*4 + {0..3}] = s_x, s_y, u_s_x, u_s_y */
+void oracle_set_marker32_replay(void *h, const float *vals, int n_steps);
 
 /* derived run parameters of main.cu:291-321,336 */
 typedef struct oracle_derived {

@@ -104,6 +104,14 @@ class Checker:
         self.lib.oracle_set_marker32_trace.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
         self.lib.oracle_set_marker32_trace(self.h, t.ctypes.data, t.shape[0])
 
+    def set_marker32_replay(self, vals):
+        """oracle port only: vals[it, m, 0:4] = (s_x, s_y, u_s_x, u_s_y) of marker 32 of cilium m
+        at step it, as the reference's CUDA build produced them (covers torn racing stores)."""
+        t = np.ascontiguousarray(vals, np.float32)
+        self.lib.oracle_set_marker32_replay.argtypes = [ctypes.c_void_p, ctypes.c_void_p,
+                                                        ctypes.c_int]
+        self.lib.oracle_set_marker32_replay(self.h, t.ctypes.data, t.shape[0])
+
     def step(self, n=1):
         rc = self._step(self.h, n)
         if rc != 0:

@@ -1,0 +1,223 @@
+"""x-slab coupling, full-size (BASELINE.json configs[1]) properties, and the driver-level run.
+Needs a B200: `pytest -m gpu`."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from checkers import (REF_FLAG_PICK_LOWEST_K, Checker, make_params, reference_tau, rel_l2)
+from cuda_iblb_11_b200 import FLAG_HALF_FORCE_BODY, Params, Solver, lib, run
+from cuda_iblb_11_b200 import slabs
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def n_gpus():
+    cudart = ctypes.CDLL("libcudart.so")
+    n = ctypes.c_int(0)
+    cudart.cudaGetDeviceCount(ctypes.byref(n))
+    return n.value
+
+
+def gather_slabs(parts, X, Y):
+    """slab-local (rho,u) in reference layout -> global arrays"""
+    rho = np.empty((Y, X))
+    ux = np.empty((Y, X))
+    uy = np.empty((Y, X))
+    for (x0, w, s) in parts:
+        r, u = s.fields()
+        rho[:, x0:x0 + w] = r.reshape(Y, w)
+        ux[:, x0:x0 + w] = u[:w * Y].reshape(Y, w)
+        uy[:, x0:x0 + w] = u[w * Y:].reshape(Y, w)
+    return rho.ravel(), np.concatenate([ux.ravel(), uy.ravel()])
+
+
+def make_local_ring(X, Y, n, devices, **kw):
+    align = kw.get("c_space", 48) if kw.get("c_num", 0) else 1
+    parts = []
+    for r in range(n):
+        x0, w = slabs.slab_range(r, n, X, align)
+        parts.append((x0, w, Solver(Params.channel(X, Y, slab_x0=x0, slab_w=w,
+                                                   device=devices[r % len(devices)], **kw))))
+    for r in range(n):
+        l, rr = slabs.ring_neighbours(r, n)
+        parts[r][2].connect_local(parts[l][2], parts[rr][2])
+    return parts
+
+
+@pytest.mark.parametrize("n_slabs,X,Y,kw", [
+    (2, 128, 64, dict(gx=1e-6, u0_amp=1e-3)),
+    (3, 96, 128, dict(gx=0.0, u0_amp=4e-3)),
+    (4, 102, 40, dict(gx=1e-6, u0_amp=1e-3)),           # generic path, uneven widths
+    (2, 288, 192, dict(c_num=6, c_fraction=6)),          # cilia straddle the slab seam
+    (3, 288, 192, dict(c_num=6, c_fraction=1)),
+    (4, 576, 192, dict(c_num=12, c_fraction=12)),
+])
+def test_slabs_on_one_gpu_are_bit_identical_to_the_whole_channel(n_slabs, X, Y, kw):
+    whole = Solver(Params.channel(X, Y, **kw))
+    parts = make_local_ring(X, Y, n_slabs, [0], **kw)
+    done = 0
+    for n in (1, 2, 9, 30):
+        for _ in range(n - done):
+            for (_, _, s) in parts:  # lockstep
+                s.step(1)
+        whole.step(n - done)
+        done = n
+        rho, u = gather_slabs(parts, X, Y)
+        r2, u2 = whole.fields()
+        assert np.array_equal(rho, r2), "rho it=%d" % n
+        assert np.array_equal(u, u2), "u it=%d" % n
+    if kw.get("c_num"):
+        q = sum(s.Q for (_, _, s) in parts)  # the flux plane lives in exactly one slab
+        assert q == whole.Q
+    for (_, _, s) in parts:
+        s.close()
+    whole.close()
+
+
+@pytest.mark.skipif("n_gpus() < 2")
+def test_slabs_across_two_gpus_same_process():
+    X, Y, kw = 256, 256, dict(gx=1e-6, u0_amp=1e-3)
+    whole = Solver(Params.channel(X, Y, device=0, **kw))
+    parts = make_local_ring(X, Y, 2, [0, 1], **kw)
+    for _ in range(20):
+        for (_, _, s) in parts:
+            s.step(1)
+    whole.step(20)
+    rho, u = gather_slabs(parts, X, Y)
+    r2, u2 = whole.fields()
+    assert np.array_equal(rho, r2) and np.array_equal(u, u2)
+
+
+@pytest.mark.skipif("n_gpus() < 2")
+def test_slabs_across_processes_ipc():
+    """one process per GPU, CUDA IPC peer stores + device flags (the bench's N>1 path)"""
+    cmd = ["python", "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", "29671",
+           os.path.join(ROOT, "tools", "slab_ipc_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "IPC SLABS OK" in r.stdout
+
+
+# ------------------------------------------------------------------------------ full size (C2)
+def test_c2_full_size_equals_narrow_oracle_channel():
+    """configs[1]: 8192x8192 forced channel.  The problem is x-invariant, so every column must
+    equal the oracle's 4x8192 channel — the full-size run checked exactly, at oracle cost 4/8192."""
+    Y, gx, u0, steps = 8192, 1e-7, 1e-3, 30
+    s = Solver(Params.channel(8192, Y, gx=gx, u0_amp=u0))
+    o = Checker("oracle", make_params(4, Y, gx=gx, u0_amp=u0, threads=4))
+    s.step(steps)
+    o.step(steps)
+    rho, u = s.fields()
+    ro, uo = o.fields()
+    rho = rho.reshape(Y, 8192)
+    ux = u[:8192 * Y].reshape(Y, 8192)
+    uy = u[8192 * Y:].reshape(Y, 8192)
+    # x-invariance is exact (same arithmetic in every column)
+    assert np.array_equal(rho, np.broadcast_to(rho[:, :1], rho.shape))
+    assert np.array_equal(ux, np.broadcast_to(ux[:, :1], ux.shape))
+    assert rel_l2(rho[:, 0], ro.reshape(Y, 4)[:, 0]) <= 1e-10
+    assert rel_l2(ux[:, 0], uo[:4 * Y].reshape(Y, 4)[:, 0]) <= 1e-10
+    assert np.abs(uy).max() <= 1e-10 * np.abs(ux).max() + np.abs(uo[4 * Y:]).max() * 2
+    s.close()
+
+
+def test_c2_full_size_mass_conservation_and_start_up_flow():
+    """no forcing: total mass conserved to the C_S-truncation drift (~1e-12/step); uniform forcing
+    from rest: away from the walls u_x grows by exactly the momentum the reference's scheme
+    injects per step, (1-1/2TAU) + 1/(2 TAU2) times g (TRT odd moments relax with 1/TAU2 while
+    the Guo prefactor uses TAU: LatticeBoltzmann.cu:56,80-81)."""
+    Y = 8192
+    s = Solver(Params.channel(8192, Y, u0_amp=2e-3))
+    m0 = s.fields()[0].sum()
+    s.step(20)
+    m1 = s.fields()[0].sum()
+    assert abs(m1 - m0) <= 1e-10 * m0
+    s.close()
+    g, n = 1e-7, 40
+    s = Solver(Params.channel(8192, Y, gx=g))
+    s.step(n)
+    rho, u = s.fields()
+    ux = u[:8192 * Y].reshape(Y, 8192)[Y // 2]
+    tau, tau2 = reference_tau()
+    # the core of the channel never feels the walls in 40 steps: plug flow, closed form below
+    o = Checker("oracle", make_params(4, 256, gx=g, threads=1))
+    o.step(n)
+    core = o.fields()[1][:4 * 256].reshape(256, 4)[128, 0]
+    assert np.abs(ux / core - 1).max() <= 1e-10
+    assert core > 0.5 * n * g
+    s.close()
+
+
+# ------------------------------------------------------------------------------ driver-level run
+def test_run_writes_the_reference_data_tree(tmp_path):
+    """iblb_run == the reference's main(): SimLog.txt, flux file, fluid/cilia snapshots
+    (main.cu:589-631, 758-790, 936-1005, 1030-1060), values checked against the oracle through the
+    reference's 6-significant-digit text format."""
+    p = Params.from_args("6 6 48 1.0 1.0 5 1.0 100 0 1".split())  # BigData on
+    p.ITERATIONS, p.INTERVAL, p.device = 41, 20, 0
+    root = str(tmp_path / "Data")
+    run(p, root)
+    raw = os.path.join(root, "Raw", "6", "6")
+    cil = os.path.join(root, "Cilia", "6", "6")
+    flux = os.path.join(root, "Flux", "6_6_48_1_1x5-flux.dat")
+    assert sorted(os.listdir(raw)) == ["0-fluid.dat", "20-fluid.dat", "40-fluid.dat", "SimLog.txt"]
+    assert sorted(os.listdir(cil)) == ["0-cilia.dat", "20-cilia.dat", "40-cilia.dat"]
+    log = open(os.path.join(raw, "SimLog.txt")).read()
+    for needle in ("Size: 288x192", "Iterations: 41", "Reynolds Number: 1",
+                   "Relaxation times: 2.8068, 0.536125", "Spatial step: 6.25e-08m",
+                   "Time step: 6.7e-07s", "Mach number: 0.0138648", "Phase Step: 6/6",
+                   "Big Data is ON", "Running on local GPU", "Total runtime: "):
+        assert needle in log, needle
+    o = Checker("oracle", make_params(288, 192, c_num=6, c_fraction=6,
+                                      flags=REF_FLAG_PICK_LOWEST_K, threads=8))
+    rows = [l.split("\t") for l in open(flux).read().splitlines()]
+    assert [r[0] for r in rows] == ["0", "0.0134", "0.0268", "0.02747"]  # it*t_scale, %g
+    qs = []
+    for n in (1, 21, 41):
+        o.step(n - o.it)
+        qs.append(o.Q)
+    for r, q in zip(rows, qs + [qs[-1]]):
+        assert float(r[1]) == pytest.approx(q * 0.0625, rel=2e-5, abs=1e-12)
+    # fluid snapshot of iteration 40: one line per node, x fastest, blank line after each row
+    lines = open(os.path.join(raw, "40-fluid.dat")).read().split("\n")
+    data = [l for l in lines if l]
+    assert len(data) == 288 * 192 and len(lines) == 288 * 192 + 192 + 1
+    rho, u = o.fields()
+    j = 37 * 288 + 101
+    x, y, ux, uy, ab, r = [float(v) for v in data[j].split("\t")]
+    s_scale = p.s_scale
+    assert x == pytest.approx(101 * 0.0625) and y == pytest.approx(37 * 0.0625)
+    assert ux == pytest.approx(u[j] * s_scale, rel=2e-5, abs=1e-9)
+    assert uy == pytest.approx(u[288 * 192 + j] * s_scale, rel=2e-5, abs=1e-9)
+    assert r == pytest.approx(rho[j], rel=2e-6)
+    cl = open(os.path.join(cil, "40-cilia.dat")).read().split("\n")
+    cdata = [l for l in cl if l]
+    assert len(cdata) == 576
+    sm, us, _, eps = o.markers()
+    k = 200
+    v = [float(t) for t in cdata[k].split("\t")]
+    assert v[0] == pytest.approx(sm[2 * k] * 0.0625, rel=2e-5)
+    assert v[1] == pytest.approx(sm[2 * k + 1] * 0.0625, rel=2e-5)
+    assert v[2] == pytest.approx(us[2 * k] * s_scale, rel=2e-5, abs=1e-9)
+    assert int(v[4]) == eps[k]
+
+
+def test_app_executable_surface(tmp_path):
+    app = os.path.join(ROOT, "app")
+    if not os.path.exists(app):
+        pytest.skip("app not built")
+    r = subprocess.run([app, "1", "6"], capture_output=True, text=True)
+    assert r.returncode == 1 and "Too few arguments! 2 entered of 10 required." in r.stdout
+    r = subprocess.run([app] + "1 3 48 1.0 1.0 5 1.0 100 0 0".split(), capture_output=True, text=True)
+    assert r.returncode == 1 and "not enough cilia in simulation!" in r.stdout
+    env = dict(os.environ, IBLB_ROOT=str(tmp_path / "D"), IBLB_ITERATIONS="30")
+    r = subprocess.run([app] + "1 6 1.0 100000 100000 100 0 0".split(), capture_output=True,
+                       text=True, env=env)  # legacy 8-value script line (app.sh:7)
+    assert r.returncode == 0, r.stderr
+    assert "Running Simulation..." in r.stdout
+    assert os.path.exists(str(tmp_path / "D" / "Flux" / "1_6_48_1_1x5-flux.dat"))

@@ -11,16 +11,16 @@ from cuda_iblb_11_b200 import FLAG_NO_GRAPH, FLAG_PICK_HIGHEST_K, Params, Solver
 
 
 def cmp_case(name, X, Y, c_num=0, steps=(1, 10), gx=0., u0=0., kinds=("oracle", "ref_cuda"),
-             flags=0):
+             flags=0, c_fraction=1):
     print("==", name, flush=True)
-    s = Solver(Params.channel(X, Y, c_num=c_num, gx=gx, u0_amp=u0, flags=flags))
+    s = Solver(Params.channel(X, Y, c_num=c_num, gx=gx, u0_amp=u0, flags=flags, c_fraction=c_fraction))
     cks = {}
     for k in kinds:
         if available(k):
             fl = 0
             if k == "oracle" and not (flags & FLAG_PICK_HIGHEST_K):
                 fl = REF_FLAG_PICK_LOWEST_K
-            cks[k] = Checker(k, make_params(X, Y, c_num=c_num, gx=gx, u0_amp=u0, flags=fl))
+            cks[k] = Checker(k, make_params(X, Y, c_num=c_num, gx=gx, u0_amp=u0, flags=fl, c_fraction=c_fraction))
     done = 0
     for n in steps:
         s.step(n - done)
@@ -45,9 +45,10 @@ def cmp_case(name, X, Y, c_num=0, steps=(1, 10), gx=0., u0=0., kinds=("oracle", 
 
 if __name__ == "__main__":
     cmp_case("c1", 288, 192, c_num=6, steps=(1, 2, 10, 20, 30))
-    cmp_case("c3", 576, 192, c_num=12, steps=(1, 10, 20))
-    a = Solver(Params.channel(288, 192, c_num=6))
-    b = Solver(Params.channel(288, 192, c_num=6, flags=FLAG_NO_GRAPH))
+    cmp_case("c1s", 288, 192, c_num=6, steps=(1, 10, 100, 1000), c_fraction=6)
+    cmp_case("c3s", 576, 192, c_num=12, steps=(1, 10, 100), c_fraction=12)
+    a = Solver(Params.channel(288, 192, c_num=6, c_fraction=6))
+    b = Solver(Params.channel(288, 192, c_num=6, c_fraction=6, flags=FLAG_NO_GRAPH))
     a.step(21)
     b.step(21)
     print("graph vs direct:", [bool(np.array_equal(x, y)) for x, y in zip(a.fields(), b.fields())],
@@ -58,3 +59,11 @@ if __name__ == "__main__":
         t = sol.last_step_seconds
         print("C1 %s: %.2f us/step, %.1f MLUPS" % (nm, t / 2000 * 1e6, 288 * 192 * 2000 / t / 1e6))
     print("C1 phases:", b.profile_phases(50))
+    for (X, Y, cn, cs) in ((576, 192, 12, 48), (8192, 192, 64, 128), (8192, 8192, 64, 128)):
+        c = Solver(Params.channel(X, Y, c_num=cn, c_space=cs, c_fraction=cn, flags=FLAG_NO_GRAPH))
+        c.step(20)
+        ph = c.profile_phases(20)
+        tot = sum(ph.values())
+        print("%dx%d %d cilia phases: %s  IB share %.1f%%" % (
+            X, Y, cn, ph, 100 * (tot - ph["lb"]) / tot))
+        c.close()
