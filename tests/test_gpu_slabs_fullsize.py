@@ -148,7 +148,10 @@ def test_c2_full_size_mass_conservation_and_start_up_flow():
     o = Checker("oracle", make_params(4, 256, gx=g, threads=1))
     o.step(n)
     core = o.fields()[1][:4 * 256].reshape(256, 4)[128, 0]
-    assert np.abs(ux / core - 1).max() <= 1e-10
+    # u = 3e-6 is a difference of O(0.1) populations: 40 steps of 1e-17 absolute rounding
+    # (FMA vs none) are 1e-10 relative to it; the absolute error is what is bounded
+    assert np.abs(ux - core).max() <= 1e-14
+    assert np.abs(ux / core - 1).max() <= 1e-9
     assert core > 0.5 * n * g
     s.close()
 
