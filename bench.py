@@ -260,7 +260,7 @@ def run_ours(a):
             "algorithmic_bytes_per_launch": BYTES_PER_LUP * nodes_local,
             "avg_launch_ms": round(1e3 * t_dev / a.steps, 4),
             "launches_of_kernel": lb_launches_per_rank,
-            "traffic": tr.get("dram_bytes_per_launch") if tr else None}
+            "traffic": tr.get("dram_bytes_per_launch") if (tr and a.workload == "c2") else None}
     out = None
     if pl.rank == 0:
         out = {
