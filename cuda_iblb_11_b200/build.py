@@ -13,7 +13,8 @@ CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libiblb.so")
 APP = os.path.join(ROOT, "app")
 
-CUDA_SOURCES = ["lb_kernels.cu", "ib_kernels.cu", "solver.cu", "step.cu", "slab.cu"]
+CUDA_SOURCES = ["lb_kernels.cu", "ib_kernels.cu", "fused_step.cu", "solver.cu", "step.cu",
+                "slab.cu"]
 HOST_SOURCES = ["params.cpp", "run.cpp"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
@@ -34,7 +35,8 @@ def _run(cmd):
 
 def build(force=False, verbose=False):
     """Compile libiblb.so and app if any source is newer.  Returns the library path."""
-    headers = [os.path.join(CSRC, h) for h in ("iblb_device.cuh", "iblb_internal.h")]
+    headers = [os.path.join(CSRC, h) for h in ("iblb_device.cuh", "iblb_internal.h",
+                                               "lb_device.cuh", "ib_device.cuh")]
     headers.append(os.path.join(ROOT, "include", "iblb.h"))
     srcs = [os.path.join(CSRC, s) for s in CUDA_SOURCES + HOST_SOURCES]
     if force or _newer(LIB, srcs + headers):

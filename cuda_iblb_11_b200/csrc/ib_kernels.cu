@@ -13,22 +13,9 @@
 //    (ImmersedBoundary.cu:178-203) at O(9 Ns) instead of O(size*Ns) work.
 // The float/double rounding points of the reference are kept on purpose (SURVEY Q3,Q6,Q7,Q14).
 #include "iblb_device.cuh"
+#include "ib_device.cuh"
 
 namespace iblb {
-
-// beat-shape coefficient tables, main.cu:56-74 ("without mucus" set): data, n fastest
-__device__ __constant__ const double kA[7 * 2 * 3] = {
-    -0.654, 0.393,  -0.097, 0.079,  0.119,  0.119,  0.009,  1.895,  -0.018, 0.158,  0.010,
-    0.003,  0.013,  0.040,  0.787,  -1.516, 0.032,  -0.302, -0.252, -0.015, 0.035,  -0.552,
-    -0.126, -0.341, 0.035,  0.006,  -0.029, -0.068, 0.202,  0.716,  -0.118, 0.142,  0.110,
-    -0.013, -0.043, 0.096,  0.263,  0.186,  -0.067, -0.032, -0.002, 0.015};
-__device__ __constant__ const double kB[7 * 2 * 3] = {
-    0.0,    0.284, 0.006,  -0.059, 0.018,  0.053,  0.009,  0.0,    0.192,  -0.050, 0.012,
-    -0.007, -0.014, -0.017, 0.0,   1.045,  0.317,  0.226,  0.004,  -0.082, -0.040, 0.0,
-    -0.499, 0.423, 0.138,  0.125,  0.075,  0.067,  0.0,    -1.017, -0.276, -0.196, -0.037,
-    0.025,  0.023, 0.0,    0.339,  -0.327, -0.114, -0.105, -0.057, -0.055};
-
-#define IBLB_PI_REF 3.14159  // main.cu:29
 
 // Per-marker shape coefficients a_n(arcl), b_n(arcl) (main.cu:109-135), once at create.
 // k_of_j[j]: the fine point that wins marker j (main.cu:158-172).  coef[j][0..13] = a_n[2n+c],
@@ -49,27 +36,6 @@ __global__ void ib_coef(const int *k_of_j, float *coef) {
         }
 }
 
-namespace {
-
-// main.cu:102-103
-__device__ __forceinline__ int beat_phase(int it, int m, int p_step, int T) {
-    return (it + m * p_step == T) ? T : (it + m * p_step) % T;
-}
-
-// main.cu:137-145 for one marker; cs[n-1] = (cos, sin)(n*2*PI*phase/T)
-__device__ __forceinline__ float2 marker_pos(const float *cf, const double2 *cs, float offset) {
-    float sx = 1. * 111 * cf[0] * 0.5 + offset;
-    float sy = 1. * 111 * cf[1] * 0.5;
-#pragma unroll
-    for (int n = 1; n < 7; n++) {
-        sx += 1. * 111 * (cf[2 * n + 0] * cs[n - 1].x + cf[14 + 2 * n + 0] * cs[n - 1].y);
-        sy += 1. * 111 * (cf[2 * n + 1] * cs[n - 1].x + cf[14 + 2 * n + 1] * cs[n - 1].y);
-    }
-    return make_float2(sx, sy);
-}
-
-}  // namespace
-
 // One block (128 threads) per cilium: positions at `it` and `it-1`, velocity, wrap, bbox.
 __global__ void __launch_bounds__(128) ib_kinematics(const IbParams p) {
     __shared__ __align__(16) double trig[24];  // [t][n][cos,sin]: t=0 current, t=1 previous
@@ -78,35 +44,17 @@ __global__ void __launch_bounds__(128) ib_kinematics(const IbParams p) {
     const int t = threadIdx.x;
     const int T = p.T;
     const int it = p.it_ptr ? *p.it_ptr : p.it;
-    if (t < 24) {
-        const int which = t / 12, r = t % 12, n = r / 2 + 1;
-        const int phase = beat_phase(it - which, m, p.p_step, T);
-        // main.cu:143: n*2.*PI*phase/T, left to right in double
-        const double arg = n * 2. * IBLB_PI_REF * phase / T;
-        trig[t] = (r & 1) ? sin(arg) : cos(arg);
-    }
+    if (t < 24) trig[t] = beat_trig(t % 12, it - t / 12, m, p.p_step, T);  // main.cu:143
     __syncthreads();
     float sx = 0.f;
     if (t < kMarkersPerCilium) {
-        const double c_space = p.c_space, c_num = p.c_num;
-        const float offset = 1. * (m - (c_num - 1) / 2.) * c_space;  // main.cu:105
-        const float *cf = p.coef + t * 28;
-        const double2 *cs0 = reinterpret_cast<const double2 *>(trig);
-        const double2 *cs1 = reinterpret_cast<const double2 *>(trig + 12);
-        const float2 b = marker_pos(cf, cs0, offset);
-        float2 v = make_float2(0.f, 0.f);
-        if (it > 0) {  // main.cu:147-151, 200-209
-            const float2 l = marker_pos(cf, cs1, offset);
-            v.x = b.x - l.x;
-            v.y = b.y - l.y;
-        }
-        // main.cu:193-198
-        sx = (c_space * c_num) / 2. + b.x;
-        if (sx < 0) sx += p.L.XDIM;
-        else if (sx > p.L.XDIM) sx -= p.L.XDIM;
-        const float sy = b.y + 1;
+        float2 sm, v;
+        marker_state(p.coef + t * 28, reinterpret_cast<const double2 *>(trig),
+                     reinterpret_cast<const double2 *>(trig + 12), m, it, p.c_space, p.c_num,
+                     p.L.XDIM, sm, v);
+        sx = sm.x;
         const int k = m * kMarkersPerCilium + t;
-        p.M.s[k] = make_float2(sx, sy);
+        p.M.s[k] = sm;
         p.M.u_s[k] = v;
     }
     // bbox of the wrapped x positions (for the spreading tiles)
@@ -124,21 +72,6 @@ __global__ void __launch_bounds__(128) ib_kinematics(const IbParams p) {
     if (t == 0)
         p.M.bbox[m] = make_float2(fminf(fminf(red_min[0], red_min[1]), red_min[2]),
                                   fmaxf(fmaxf(red_max[0], red_max[1]), red_max[2]));
-}
-
-// one factor of the 3-point delta, ImmersedBoundary.cu:21-81 (truncated prefactors, float |r|,
-// double body, float result)
-__device__ __forceinline__ float delta_1d(float r) {
-    double a = 0., b = 0., d = 0.;
-    int c = 0;
-    if (r <= 1.5) {
-        if (r <= 0.5) {
-            a = 0.33333; b = 1.; c = 1; d = r;
-        } else {
-            a = 0.16667; b = 5. - 3. * r; c = -1; d = 1 - r;
-        }
-    }
-    return a * (b + c * sqrt(-3. * d * d + 1));
 }
 
 // Warp per marker: epsilon (main.cu:217-248), then F_s (ImmersedBoundary.cu:94-133) with the
@@ -166,44 +99,7 @@ __global__ void __launch_bounds__(256) ib_interpolate(const IbParams p) {
 
     // ---- lanes 0..8: support node i of the marker ----
     double tx = 0., ty = 0.;
-    if (lane < 9) {
-        const double xs = sm.x, ys = sm.y;
-        const int x0 = (int)nearbyint(xs), y0 = (int)nearbyint(ys);
-        const int x = x0 + kCx[lane], y = y0 + kCy[lane];
-        // the reference indexes j = y*XDIM + x without wrapping (ImmersedBoundary.cu:119-122):
-        // x = -1 lands on (XDIM-1, y-1), x = XDIM on (0, y+1)
-        const long long j = (long long)y * L.XDIM + x;
-        if (j >= 0 && j < (long long)L.XDIM * L.YDIM) {
-            const int ya = (int)(j / L.XDIM), xa = (int)(j - (long long)ya * L.XDIM);
-            // global column -> a local column whose three source columns are present
-            int xl = xa - L.x0;
-            if (xl < -(L.G - 1)) xl += L.XDIM;
-            else if (xl > L.W + L.G - 2) xl -= L.XDIM;
-            if (xl >= -(L.G - 1) && xl <= L.W + L.G - 2) {
-                double f[9];
-#pragma unroll
-                for (int i = 0; i < 9; i++) {
-                    int pi = i, xsrc = xl - kCx[i], ysrc = ya - kCy[i];
-                    if (ysrc < 0) {
-                        pi = (i == 2) ? 4 : (i == 5) ? 7 : 8;
-                        xsrc = xl; ysrc = ya;
-                    } else if (ysrc >= L.YDIM) {
-                        pi = (i == 4) ? 2 : (i == 7) ? 6 : 5;
-                        xsrc = xl; ysrc = ya;
-                    }
-                    f[i] = p.src[pi * L.plane + L.off(xsrc, ysrc)];
-                }
-                const double rho = f[0] + f[1] + f[2] + f[3] + f[4] + f[5] + f[6] + f[7] + f[8];
-                const double ux = (f[1] - f[3] + f[5] - f[6] - f[7] + f[8]) / rho;
-                const double uy = (f[2] - f[4] + f[5] + f[6] - f[7] - f[8]) / rho;
-                const float dlx = delta_1d(fabsf(x - sm.x));
-                const float dly = delta_1d(fabsf(y - sm.y));
-                const double del = dlx * dly;  // float product (ImmersedBoundary.cu:78)
-                tx = 2. * (1. * 1. * del) * rho * (us.x - ux);  // :126
-                ty = 2. * (1. * 1. * del) * rho * (us.y - uy);  // :127
-            }
-        }
-    }
+    if (lane < 9) interp_term(L, p.src, sm, us, lane, tx, ty);
     // F_s is a float re-rounded after each of the nine terms, fixed order (Q6)
     float Fx = 0.f, Fy = 0.f;
 #pragma unroll

@@ -79,4 +79,19 @@ struct IbParams {
     int band_rows, band_ld;
 };
 
+// fused IB+LB step (fused_step.cu)
+constexpr int kFusedMaxCilia = 16;  // cilia whose marker states one band tile may need
+constexpr int kFusedMaxList = 512;  // markers whose support can touch one 8x64 tile
+
+struct FusedParams {
+    LbParams lb;
+    const float *coef;       // as IbParams::coef
+    int c_num, c_space, T, p_step, r_max;
+    int it, it_off;          // iteration = (it_ptr ? *it_ptr : it) + it_off
+    const int *it_ptr;
+    float reach;             // bound on |marker x - translated base of its cilium| (from coef)
+    int band_rows;           // rows that can receive IB force (multiple of 64)
+    int *err;                // set non-zero when a tile exceeds kFusedMaxCilia / kFusedMaxList
+};
+
 }  // namespace iblb

@@ -30,6 +30,8 @@ __global__ void ib_coef(const int *k_of_j, float *coef);
 __global__ void ib_kinematics(const IbParams p);
 __global__ void ib_interpolate(const IbParams p);
 __global__ void ib_spread(const IbParams p);
+__global__ void iblb_fused_step(const FusedParams p);
+__global__ void it_advance(int *it_ptr, int by);
 __global__ void slab_wait(const volatile int *flag_l, const volatile int *flag_r, int need);
 __global__ void slab_signal(int *left_flag, int *right_flag, int value);
 
@@ -52,6 +54,12 @@ struct iblb_solver {
     double *band;
     int band_rows, band_ld;
     int *it_dev;               // device copy of `it` read by the graph-captured kinematics
+    // fused IB+LB step (single launch per iteration)
+    bool fuse_ok;              // geometry allows it (whole channel, YDIM % 64 == 0, reach bounds)
+    bool ib_stale;             // marker arrays / force band not materialised for the last step
+    float reach_x, reach_y;    // bounds on the marker excursion from the cilium base
+    int *err_dev;
+    cudaGraphExec_t fused_graph;  // kFusedBatch iterations + it_advance
     // flux
     double *qacc, *qpart;
     int nq;

@@ -1,0 +1,166 @@
+// Device helpers shared by the LB kernels (lb_kernels.cu) and the fused IB+LB step (fused_step.cu):
+// moments, TRT collision with Guo forcing, vector load/shuffle helpers.  sm_100a only.
+#pragma once
+#include "iblb_device.cuh"
+
+namespace iblb {
+namespace {
+
+constexpr double kIcs2 = 1.0 / (kCs * kCs);                     // 1/cs^2
+constexpr double kIcs4 = 1.0 / (kCs * kCs * kCs * kCs);         // 1/cs^4
+constexpr double kIcs4h = 1.0 / (2.0 * kCs * kCs * kCs * kCs);  // 1/(2 cs^4)
+constexpr double kIcs2h = 1.0 / (2.0 * kCs * kCs);              // 1/(2 cs^2)
+constexpr double kW0 = 4.0 / 9.0, kW1 = 1.0 / 9.0, kW2 = 1.0 / 36.0;
+
+// reflection partners used by the wall rules (pull form)
+//   y == 0      : f2 <- f4, f5 <- f7, f6 <- f8   (same node)
+//   y == YDIM-1 : f4 <- f2, f7 <- f6, f8 <- f5   (same node)
+
+__device__ __forceinline__ double shfl_up1(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
+__device__ __forceinline__ double shfl_dn1(double v) {
+    return __shfl_down_sync(0xffffffffu, v, 1);
+}
+
+__device__ __forceinline__ double2 ldg2(const double *p) {
+    return __ldg(reinterpret_cast<const double2 *>(p));
+}
+
+// TRT relaxation of one antiparallel pair (a = +c, b = -c) plus the Guo term.
+// LatticeBoltzmann.cu:88-134 with f0 split into its even/odd parts analytically.
+__device__ __forceinline__ void relax_pair(double &fa, double &fb, double rw, double cu,
+                                           double base, double wp, double wm, double kw,
+                                           double cF, double uF, bool forced) {
+    const double f0p = rw * (base + cu * cu * kIcs4h);
+    const double f0m = rw * (cu * kIcs2);
+    const double fp = 0.5 * (fa + fb);
+    const double fm = 0.5 * (fa - fb);
+    const double A = wp * (fp - f0p);
+    const double B = wm * (fm - f0m);
+    double na = fa - A - B;
+    double nb = fb - A + B;
+    if (forced) {
+        const double S = kw * (cu * cF * kIcs4 - uF * kIcs2);
+        const double D = kw * (cF * kIcs2);
+        na += S + D;
+        nb += S - D;
+    }
+    fa = na;
+    fb = nb;
+}
+
+// moments (LatticeBoltzmann.cu:396-405, summation order i = 0..8), half-force velocity
+// (ImmersedBoundary.cu:249-255), then equilibrium + forcing + TRT.  Returns u_x.
+__device__ __forceinline__ double collide_node(double (&f)[9], double Fx, double Fy, bool forced,
+                                               const LbParams &p) {
+    const double rho = f[0] + f[1] + f[2] + f[3] + f[4] + f[5] + f[6] + f[7] + f[8];
+    const double mx = f[1] - f[3] + f[5] - f[6] - f[7] + f[8];
+    const double my = f[2] - f[4] + f[5] + f[6] - f[7] - f[8];
+    const double ir = 1.0 / rho;
+    const double ux = (mx + p.half * Fx) * ir;
+    const double uy = (my + p.half * Fy) * ir;
+    const double base = 1.0 - (ux * ux + uy * uy) * kIcs2h;
+    const double wp = p.omega_plus, wm = p.omega_minus;
+    const double uF = ux * Fx + uy * Fy;
+    const double k1 = p.kforce * kW1, k2 = p.kforce * kW2;
+    const double r1 = rho * kW1, r2 = rho * kW2;
+    // rest population: no force term (LatticeBoltzmann.cu:86)
+    f[0] = f[0] - wp * (f[0] - rho * kW0 * base);
+    relax_pair(f[1], f[3], r1, ux, base, wp, wm, k1, Fx, uF, forced);
+    relax_pair(f[2], f[4], r1, uy, base, wp, wm, k1, Fy, uF, forced);
+    relax_pair(f[5], f[7], r2, ux + uy, base, wp, wm, k2, Fx + Fy, uF, forced);
+    relax_pair(f[6], f[8], r2, uy - ux, base, wp, wm, k2, Fy - Fx, uF, forced);
+    return ux;
+}
+
+__device__ __forceinline__ void store_remote2(const Remote &r, int col, int y0, int i, double2 v) {
+    *reinterpret_cast<double2 *>(r.base + (long long)i * r.plane + (long long)(col + r.G) * r.ld +
+                                 y0) = v;
+}
+
+
+// The nine populations two vertically adjacent nodes (y0, y0+1) of column x pull, as loaded:
+// one aligned 128-bit load per population from the column it streams from, plus the values from
+// the row below lane 0 / above lane 31 of the warp (walls folded in).
+struct Pulled {
+    double2 v[9];
+    double e2, e5, e6, e4, e7, e8;
+};
+
+__device__ __forceinline__ void load_pulled(const Lattice &L, const double *__restrict__ src, int x,
+                                            int y0, int lane, Pulled &q) {
+    const long long P = L.plane;
+    const long long cm = L.off(x - 1, y0), c0 = L.off(x, y0), cp = L.off(x + 1, y0);
+    const bool at_bottom = (y0 == 0);
+    const bool at_top = (y0 + 2 == L.YDIM);
+    q.v[0] = ldg2(src + 0 * P + c0);
+    q.v[1] = ldg2(src + 1 * P + cm);  // c = (+1, 0): from x-1
+    q.v[2] = ldg2(src + 2 * P + c0);  // c = ( 0,+1): from y-1
+    q.v[3] = ldg2(src + 3 * P + cp);  // c = (-1, 0): from x+1
+    q.v[4] = ldg2(src + 4 * P + c0);  // c = ( 0,-1): from y+1
+    q.v[5] = ldg2(src + 5 * P + cm);  // c = (+1,+1)
+    q.v[6] = ldg2(src + 6 * P + cp);  // c = (-1,+1)
+    q.v[7] = ldg2(src + 7 * P + cp);  // c = (-1,-1)
+    q.v[8] = ldg2(src + 8 * P + cm);  // c = (+1,-1)
+    q.e2 = q.e5 = q.e6 = q.e4 = q.e7 = q.e8 = 0.;
+    if (lane == 0) {
+        if (at_bottom) {
+            q.e2 = q.v[4].x;  // f2(x,0) <- f4(x,0): already loaded (same column, row y0)
+            q.e5 = __ldg(src + 7 * P + c0);
+            q.e6 = __ldg(src + 8 * P + c0);
+        } else {
+            q.e2 = __ldg(src + 2 * P + c0 - 1);
+            q.e5 = __ldg(src + 5 * P + cm - 1);
+            q.e6 = __ldg(src + 6 * P + cp - 1);
+        }
+    }
+    if (lane == 31) {
+        if (at_top) {
+            q.e4 = q.v[2].y;  // f4(x,Y-1) <- f2(x,Y-1)
+            q.e7 = __ldg(src + 6 * P + c0 + 1);
+            q.e8 = __ldg(src + 5 * P + c0 + 1);
+        } else {
+            q.e4 = __ldg(src + 4 * P + c0 + 2);
+            q.e7 = __ldg(src + 7 * P + cp + 2);
+            q.e8 = __ldg(src + 8 * P + cm + 2);
+        }
+    }
+}
+
+// shift the six populations with c_y != 0 by one row in registers: a = node y0, b = node y0+1
+__device__ __forceinline__ void shift_pulled(const Pulled &q, int lane, double (&a)[9],
+                                             double (&b)[9]) {
+    a[0] = q.v[0].x; b[0] = q.v[0].y;
+    a[1] = q.v[1].x; b[1] = q.v[1].y;
+    a[3] = q.v[3].x; b[3] = q.v[3].y;
+    double t;
+    t = shfl_up1(q.v[2].y); a[2] = lane == 0 ? q.e2 : t; b[2] = q.v[2].x;
+    t = shfl_up1(q.v[5].y); a[5] = lane == 0 ? q.e5 : t; b[5] = q.v[5].x;
+    t = shfl_up1(q.v[6].y); a[6] = lane == 0 ? q.e6 : t; b[6] = q.v[6].x;
+    t = shfl_dn1(q.v[4].x); a[4] = q.v[4].y; b[4] = lane == 31 ? q.e4 : t;
+    t = shfl_dn1(q.v[7].x); a[7] = q.v[7].y; b[7] = lane == 31 ? q.e7 : t;
+    t = shfl_dn1(q.v[8].x); a[8] = q.v[8].y; b[8] = lane == 31 ? q.e8 : t;
+}
+
+// stores of one thread's two nodes: own buffer + (boundary columns) the neighbours' ghost columns
+__device__ __forceinline__ void store_pair(const LbParams &p, int x, int y0, const double (&a)[9],
+                                           const double (&b)[9]) {
+    const Lattice &L = p.L;
+    const long long c0 = L.off(x, y0);
+    double *__restrict__ dst = p.dst;
+#pragma unroll
+    for (int i = 0; i < 9; i++)
+        *reinterpret_cast<double2 *>(dst + i * L.plane + c0) = make_double2(a[i], b[i]);
+    if (x < p.left.G) {
+#pragma unroll
+        for (int i = 0; i < 9; i++)
+            store_remote2(p.left, p.left.W + x, y0, i, make_double2(a[i], b[i]));
+    }
+    if (x >= L.W - p.right.G) {
+#pragma unroll
+        for (int i = 0; i < 9; i++)
+            store_remote2(p.right, x - L.W, y0, i, make_double2(a[i], b[i]));
+    }
+}
+
+}  // namespace
+}  // namespace iblb

@@ -18,83 +18,9 @@
 // columns store their results a second time into the neighbour's ghost columns (a peer
 // pointer over NVLink when the neighbour is another GPU).
 #include "iblb_device.cuh"
+#include "lb_device.cuh"
 
 namespace iblb {
-
-namespace {
-
-constexpr double kIcs2 = 1.0 / (kCs * kCs);                     // 1/cs^2
-constexpr double kIcs4 = 1.0 / (kCs * kCs * kCs * kCs);         // 1/cs^4
-constexpr double kIcs4h = 1.0 / (2.0 * kCs * kCs * kCs * kCs);  // 1/(2 cs^4)
-constexpr double kIcs2h = 1.0 / (2.0 * kCs * kCs);              // 1/(2 cs^2)
-constexpr double kW0 = 4.0 / 9.0, kW1 = 1.0 / 9.0, kW2 = 1.0 / 36.0;
-
-// reflection partners used by the wall rules (pull form)
-//   y == 0      : f2 <- f4, f5 <- f7, f6 <- f8   (same node)
-//   y == YDIM-1 : f4 <- f2, f7 <- f6, f8 <- f5   (same node)
-
-__device__ __forceinline__ double shfl_up1(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
-__device__ __forceinline__ double shfl_dn1(double v) {
-    return __shfl_down_sync(0xffffffffu, v, 1);
-}
-
-__device__ __forceinline__ double2 ldg2(const double *p) {
-    return __ldg(reinterpret_cast<const double2 *>(p));
-}
-
-// TRT relaxation of one antiparallel pair (a = +c, b = -c) plus the Guo term.
-// LatticeBoltzmann.cu:88-134 with f0 split into its even/odd parts analytically.
-__device__ __forceinline__ void relax_pair(double &fa, double &fb, double rw, double cu,
-                                           double base, double wp, double wm, double kw,
-                                           double cF, double uF, bool forced) {
-    const double f0p = rw * (base + cu * cu * kIcs4h);
-    const double f0m = rw * (cu * kIcs2);
-    const double fp = 0.5 * (fa + fb);
-    const double fm = 0.5 * (fa - fb);
-    const double A = wp * (fp - f0p);
-    const double B = wm * (fm - f0m);
-    double na = fa - A - B;
-    double nb = fb - A + B;
-    if (forced) {
-        const double S = kw * (cu * cF * kIcs4 - uF * kIcs2);
-        const double D = kw * (cF * kIcs2);
-        na += S + D;
-        nb += S - D;
-    }
-    fa = na;
-    fb = nb;
-}
-
-// moments (LatticeBoltzmann.cu:396-405, summation order i = 0..8), half-force velocity
-// (ImmersedBoundary.cu:249-255), then equilibrium + forcing + TRT.  Returns u_x.
-__device__ __forceinline__ double collide_node(double (&f)[9], double Fx, double Fy, bool forced,
-                                               const LbParams &p) {
-    const double rho = f[0] + f[1] + f[2] + f[3] + f[4] + f[5] + f[6] + f[7] + f[8];
-    const double mx = f[1] - f[3] + f[5] - f[6] - f[7] + f[8];
-    const double my = f[2] - f[4] + f[5] + f[6] - f[7] - f[8];
-    const double ir = 1.0 / rho;
-    const double ux = (mx + p.half * Fx) * ir;
-    const double uy = (my + p.half * Fy) * ir;
-    const double base = 1.0 - (ux * ux + uy * uy) * kIcs2h;
-    const double wp = p.omega_plus, wm = p.omega_minus;
-    const double uF = ux * Fx + uy * Fy;
-    const double k1 = p.kforce * kW1, k2 = p.kforce * kW2;
-    const double r1 = rho * kW1, r2 = rho * kW2;
-    // rest population: no force term (LatticeBoltzmann.cu:86)
-    f[0] = f[0] - wp * (f[0] - rho * kW0 * base);
-    relax_pair(f[1], f[3], r1, ux, base, wp, wm, k1, Fx, uF, forced);
-    relax_pair(f[2], f[4], r1, uy, base, wp, wm, k1, Fy, uF, forced);
-    relax_pair(f[5], f[7], r2, ux + uy, base, wp, wm, k2, Fx + Fy, uF, forced);
-    relax_pair(f[6], f[8], r2, uy - ux, base, wp, wm, k2, Fy - Fx, uF, forced);
-    return ux;
-}
-
-__device__ __forceinline__ void store_remote2(const Remote &r, int col, int y0, int i, double2 v) {
-    *reinterpret_cast<double2 *>(r.base + (long long)i * r.plane + (long long)(col + r.G) * r.ld +
-                                 y0) = v;
-}
-
-}  // namespace
 
 // Fast path: YDIM % 64 == 0.  grid = ceil(W*YDIM/2 / 256), block = 256.
 __global__ void __launch_bounds__(256, 3) lb_fused_v2(const LbParams p) {

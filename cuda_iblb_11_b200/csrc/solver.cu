@@ -100,6 +100,7 @@ static int init_state(iblb_solver *s, const double *rho_dev, const double *u_dev
     IBLB_CUDA(cudaMemsetAsync(s->qacc, 0, sizeof(double) * s->nq, s->stream));
     if (s->it_dev) IBLB_CUDA(cudaMemsetAsync(s->it_dev, 0, sizeof(int), s->stream));
     s->cur = 0;
+    s->ib_stale = false;
     s->flag_base += (int)s->it;  // all slabs reset together: later flag values stay above old ones
     s->it = 0;
     IBLB_CUDA(cudaStreamSynchronize(s->stream));
@@ -183,6 +184,8 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
         TRY(cudaMalloc((void **)&s->coef, sizeof(float) * kMarkersPerCilium * 28));
         TRY(cudaMalloc((void **)&s->k_of_j_dev, sizeof(int) * kMarkersPerCilium));
         TRY(cudaMalloc((void **)&s->it_dev, sizeof(int)));
+        TRY(cudaMalloc((void **)&s->err_dev, sizeof(int)));
+        if (rc == IBLB_OK) TRY(cudaMemset(s->err_dev, 0, sizeof(int)));
         if (rc == IBLB_OK) {
             TRY(cudaMemset(s->M.s, 0, sizeof(float2) * s->Ns));
             TRY(cudaMemset(s->M.u_s, 0, sizeof(float2) * s->Ns));
@@ -193,6 +196,25 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
                            cudaMemcpyHostToDevice));
             ib_coef<<<1, 128, 0, s->stream>>>(s->k_of_j_dev, s->coef);
             TRY(cudaGetLastError());
+            // rigorous bounds on the marker excursion from the cilium base, from the coefficient
+            // table (main.cu:137-145): |x| <= 111(|a_0x|/2 + sum_n sqrt(a_nx^2 + b_nx^2))
+            std::vector<float> cf(kMarkersPerCilium * 28);
+            TRY(cudaMemcpyAsync(cf.data(), s->coef, sizeof(float) * cf.size(),
+                                cudaMemcpyDeviceToHost, s->stream));
+            TRY(cudaStreamSynchronize(s->stream));
+            double rx = 0., ry = 0.;
+            for (int j = 0; j < kMarkersPerCilium && rc == IBLB_OK; j++) {
+                const float *c = cf.data() + j * 28;
+                double bx = 111. * fabs((double)c[0]) * 0.5, by = 111. * fabs((double)c[1]) * 0.5;
+                for (int n = 1; n < 7; n++) {
+                    bx += 111. * hypot((double)c[2 * n], (double)c[14 + 2 * n]);
+                    by += 111. * hypot((double)c[2 * n + 1], (double)c[14 + 2 * n + 1]);
+                }
+                rx = bx > rx ? bx : rx;
+                ry = by > ry ? by : ry;
+            }
+            s->reach_x = (float)(rx + 0.5);
+            s->reach_y = (float)(ry + 1.0 + 0.5);  // + the translation of main.cu:198
         }
     }
 #undef TRY
@@ -207,6 +229,15 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
     const int xq = (int)p.XDIM - 5 - L.x0;
     s->xq_local = xq;
     s->flux_on = (p.c_num > 0 || (p.flags & IBLB_FLAG_HALF_FORCE_BODY)) && xq >= 0 && xq < L.W;
+    // single-launch fused IB+LB step: whole channel on this GPU, vector path, every tile's cilia
+    // set fits the kernel's shared-memory slots, markers stay inside the force band
+    if (p.c_num > 0) {
+        const int r_max = (int)(2 * kMarkersPerCilium / (double)p.c_space);
+        const int span = (int)((2. * s->reach_x + 11.) / p.c_space) + 2;
+        s->fuse_ok = !slab && s->vec2 && !(p.flags & IBLB_FLAG_NO_FUSE) &&
+                     (span + r_max - 1 <= kFusedMaxCilia || p.c_num <= (unsigned)kFusedMaxCilia) &&
+                     s->reach_y + 1.5f < (float)s->band_rows;
+    }
     // a lone solver is periodic with itself
     for (int b = 0; b < 2; b++) {
         Remote self{s->buf[b], L.plane, L.ld, L.G, L.W};
@@ -232,6 +263,8 @@ int iblb_destroy(iblb_solver *s) {
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
+    if (s->fused_graph) cudaGraphExecDestroy(s->fused_graph);
+    cudaFree(s->err_dev);
     for (int f = 0; f < 2; f++) {
         for (int b = 0; b < 2; b++)
             if (s->nb_mapped[f][b]) cudaIpcCloseMemHandle(s->nb_mapped[f][b]);

@@ -14,6 +14,41 @@ using namespace iblb;
 
 namespace {
 
+constexpr unsigned kFusedBatch = 8;  // iterations per captured batch of the fused step (even)
+
+FusedParams make_fused_params(const iblb_solver *s, int src_idx) {
+    FusedParams q;
+    memset(&q, 0, sizeof q);
+    q.lb = make_lb_params(s, src_idx);
+    q.lb.band = nullptr;  // the force never goes through memory
+    q.coef = s->coef;
+    q.c_num = (int)s->p.c_num;
+    q.c_space = (int)s->p.c_space;
+    q.T = (int)s->p.T;
+    q.p_step = s->p.p_step;
+    q.r_max = (int)(2 * kMarkersPerCilium / (double)s->p.c_space);  // main.cu:185
+    q.it = (int)s->it;
+    q.it_off = 0;
+    q.it_ptr = nullptr;
+    q.reach = s->reach_x;
+    q.band_rows = s->band_rows;
+    q.err = s->err_dev;
+    return q;
+}
+
+bool fused_path(const iblb_solver *s) {
+    const bool coupled = s->connected && !(s->self_left && s->self_right);
+    return s->p.c_num > 0 && s->fuse_ok && !coupled;
+}
+
+int launch_fused(iblb_solver *s, FusedParams &q, cudaStream_t st, unsigned long long &launches) {
+    dim3 g((unsigned)(s->L.YDIM / 64), (unsigned)((s->L.W + 7) / 8));
+    iblb_fused_step<<<g, 256, 0, st>>>(q);
+    launches += 1;
+    IBLB_CUDA(cudaGetLastError());
+    return IBLB_OK;
+}
+
 struct PhaseEvents {
     cudaEvent_t e[5];
 };
@@ -51,7 +86,7 @@ int launch_lb(iblb_solver *s, const LbParams &q, cudaStream_t st, unsigned long 
 // One iteration: [slab wait] -> kinematics -> interpolate -> spread -> fused LB (boundary columns
 // first + signal, then interior, when coupled to other GPUs).
 int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEvents *pe,
-                      unsigned long long &launches) {
+                      unsigned long long &launches, int graph_it_off = 0) {
     const int src = s->cur;
     const bool coupled = s->connected && !(s->self_left && s->self_right);
     const bool local = coupled && s->peer[0] != nullptr;
@@ -65,6 +100,20 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         launches += 1;
     }
     if (pe) cudaEventRecord(pe->e[0], st);
+    if (!pe && fused_path(s)) {
+        FusedParams q = make_fused_params(s, src);
+        if (graph_mode) {
+            q.it_ptr = s->it_dev;
+            q.it = 0;
+            q.it_off = graph_it_off;
+        }
+        int rc = launch_fused(s, q, st, launches);
+        if (rc) return rc;
+        s->ib_stale = true;
+        s->cur ^= 1;
+        s->it += 1;
+        return IBLB_OK;
+    }
     if (s->p.c_num > 0) {
         IbParams ib = make_ib_params(s, src);
         if (graph_mode) ib.it_ptr = s->it_dev;
@@ -76,6 +125,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         ib_spread<<<g, 256, 0, st>>>(ib);
         launches += 3;
         IBLB_CUDA(cudaGetLastError());
+        s->ib_stale = false;
     } else if (pe) {
         cudaEventRecord(pe->e[1], st);
         cudaEventRecord(pe->e[2], st);
@@ -138,6 +188,61 @@ int build_graph(iblb_solver *s) {
     return IBLB_OK;
 }
 
+// kFusedBatch fused iterations reading the iteration number from device memory, then it_advance
+int build_fused_graph(iblb_solver *s) {
+    cudaGraph_t graph = nullptr;
+    const int cur0 = s->cur;
+    const unsigned it0 = s->it;
+    unsigned long long dummy = 0;
+    IBLB_CUDA(cudaStreamBeginCapture(s->stream, cudaStreamCaptureModeThreadLocal));
+    int rc = IBLB_OK;
+    for (unsigned i = 0; i < kFusedBatch && rc == IBLB_OK; i++)
+        rc = enqueue_iteration(s, s->stream, true, nullptr, dummy, (int)i);
+    if (rc == IBLB_OK) it_advance<<<1, 32, 0, s->stream>>>(s->it_dev, (int)kFusedBatch);
+    cudaError_t e = cudaStreamEndCapture(s->stream, &graph);
+    s->cur = cur0;
+    s->it = it0;
+    if (rc != IBLB_OK) {
+        if (graph) cudaGraphDestroy(graph);
+        return rc;
+    }
+    if (e != cudaSuccess) return cuda_fail(e, "cudaStreamEndCapture");
+    e = cudaGraphInstantiate(&s->fused_graph, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGraphInstantiate");
+    return IBLB_OK;
+}
+
+// the fused step keeps the IB state in shared memory only: rebuild the marker arrays and the force
+// band of the last completed iteration with the stand-alone kernels when somebody asks for them
+int materialise_ib(iblb_solver *s) {
+    if (!s->ib_stale || s->p.c_num == 0 || s->it == 0) return IBLB_OK;
+    IbParams ib = make_ib_params(s, s->cur ^ 1);
+    ib.it = (int)s->it - 1;
+    ib_kinematics<<<ib.c_num, 128, 0, s->stream>>>(ib);
+    ib_interpolate<<<(ib.Ns + 7) / 8, 256, 0, s->stream>>>(ib);
+    dim3 g((s->L.W + kSpreadTileX - 1) / kSpreadTileX, s->band_rows / kSpreadTileY);
+    ib_spread<<<g, 256, 0, s->stream>>>(ib);
+    IBLB_CUDA(cudaGetLastError());
+    s->ib_stale = false;
+    return IBLB_OK;
+}
+
+int check_device_flag(iblb_solver *s) {
+    if (!s->err_dev) return IBLB_OK;
+    int flag = 0;
+    IBLB_CUDA(cudaMemcpyAsync(&flag, s->err_dev, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+    IBLB_CUDA(cudaStreamSynchronize(s->stream));
+    if (flag != 0) {
+        set_error(flag == 1 ? "fused step: a tile needs more cilia than kFusedMaxCilia "
+                              "(use IBLB_FLAG_NO_FUSE)"
+                            : "fused step: more markers touch a tile than kFusedMaxList "
+                              "(use IBLB_FLAG_NO_FUSE)");
+        return IBLB_EINVAL;
+    }
+    return IBLB_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -157,7 +262,27 @@ int iblb_step(iblb_solver *s, unsigned n_steps) {
     const bool use_graph = !(s->p.flags & IBLB_FLAG_NO_GRAPH) && !coupled && nodes <= (1 << 22) &&
                            n_steps >= 4;
     unsigned left = n_steps;
-    if (use_graph) {
+    if (use_graph && fused_path(s)) {
+        if (s->cur != 0 && left > 0) {
+            int rc = enqueue_iteration(s, st, false, nullptr, launches);
+            if (rc) return rc;
+            left--;
+        }
+        if (left >= kFusedBatch) {
+            if (!s->fused_graph) {
+                int rc = build_fused_graph(s);
+                if (rc) return rc;
+            }
+            IBLB_CUDA(cudaMemcpyAsync(s->it_dev, &s->it, sizeof(int), cudaMemcpyHostToDevice, st));
+            while (left >= kFusedBatch) {
+                IBLB_CUDA(cudaGraphLaunch(s->fused_graph, st));
+                s->it += kFusedBatch;
+                left -= kFusedBatch;
+                launches += kFusedBatch + 1;
+            }
+            s->ib_stale = true;
+        }
+    } else if (use_graph) {
         if (s->cur != 0) {
             int rc = enqueue_iteration(s, st, false, nullptr, launches);
             if (rc) return rc;
@@ -242,6 +367,11 @@ int iblb_profile_phases(iblb_solver *s, unsigned reps, double *t_kin, double *t_
 // that iteration pulled from (the step wrote the other one) ----
 static int run_moments(iblb_solver *s, double *rho, double *u, double *f, double *force) {
     IBLB_CUDA(cudaSetDevice(s->device));
+    {
+        int rc = check_device_flag(s);
+        if (rc == IBLB_OK) rc = materialise_ib(s);  // u and force need the force band
+        if (rc) return rc;
+    }
     const size_t size = (size_t)s->L.W * s->L.YDIM;
     const size_t n_out = (rho ? size : 0) + (u ? 2 * size : 0) + (f ? 9 * size : 0) +
                          (force ? 2 * size : 0);
@@ -294,6 +424,11 @@ int iblb_get_markers(iblb_solver *s, float *pos, float *vel, float *force, int *
     if (!s) return IBLB_EINVAL;
     if (s->Ns == 0) return IBLB_OK;
     IBLB_CUDA(cudaSetDevice(s->device));
+    {
+        int rc = check_device_flag(s);
+        if (rc == IBLB_OK) rc = materialise_ib(s);
+        if (rc) return rc;
+    }
     IBLB_CUDA(cudaStreamSynchronize(s->stream));
     const size_t nb = sizeof(float2) * s->Ns;
     if (pos) IBLB_CUDA(cudaMemcpy(pos, s->M.s, nb, cudaMemcpyDeviceToHost));
@@ -306,6 +441,10 @@ int iblb_get_markers(iblb_solver *s, float *pos, float *vel, float *force, int *
 int iblb_get_flux(iblb_solver *s, double *Q) {
     if (!s || !Q) return IBLB_EINVAL;
     IBLB_CUDA(cudaSetDevice(s->device));
+    {
+        int rc = check_device_flag(s);
+        if (rc) return rc;
+    }
     std::vector<double> part(s->nq);
     IBLB_CUDA(cudaMemcpyAsync(part.data(), s->qacc, sizeof(double) * s->nq, cudaMemcpyDeviceToHost,
                               s->stream));

@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(_PKG, "libiblb.so")
 FLAG_HALF_FORCE_BODY = 1
 FLAG_PICK_HIGHEST_K = 2
 FLAG_NO_GRAPH = 4
+FLAG_NO_FUSE = 8
 
 IPC_HANDLE_BYTES = 64
 

@@ -41,6 +41,9 @@ extern "C" {
                                         95 of 96 markers per cilium; marker 32's two candidates
                                         sit in different warps and its winner varies per step) */
 #define IBLB_FLAG_NO_GRAPH 4u        /* launch kernels directly instead of CUDA-graph batches */
+#define IBLB_FLAG_NO_FUSE 8u         /* keep the immersed-boundary pre-pass as separate kernels
+                                        (kinematics, interpolate, spread) instead of the single
+                                        fused IB+LB launch per iteration; same results bit for bit */
 
 typedef struct iblb_params {
     /* --- the ten driver arguments, main.cu:291-296 --- */

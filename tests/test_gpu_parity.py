@@ -25,8 +25,8 @@ import pytest
 
 from checkers import (REF_FLAG_HALF_FORCE_BODY, REF_FLAG_PICK_LOWEST_K, Checker, make_params,
                       reference_tau, rel_l2)
-from cuda_iblb_11_b200 import (FLAG_HALF_FORCE_BODY, FLAG_NO_GRAPH, FLAG_PICK_HIGHEST_K, Params,
-                               Solver)
+from cuda_iblb_11_b200 import (FLAG_HALF_FORCE_BODY, FLAG_NO_FUSE, FLAG_NO_GRAPH,
+                               FLAG_PICK_HIGHEST_K, Params, Solver)
 
 pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
@@ -245,9 +245,36 @@ def test_graph_replay_equals_direct_launches():
         for x, y in zip(a.markers(), b.markers()):
             assert np.array_equal(x, y)
         assert a.Q == b.Q
-    assert a.last_step_launches == b.last_step_launches
     a.close()
     b.close()
+
+
+@pytest.mark.parametrize("c_num,c_space,c_fraction,Y", [
+    (6, 48, 1, 192), (6, 48, 6, 192), (12, 48, 5, 192), (12, 48, 12, 256), (4, 64, 3, 192),
+    (16, 128, 16, 192), (5, 40, 2, 192), (2, 192, 1, 128),
+])
+def test_fused_single_launch_step_equals_separate_kernels(c_num, c_space, c_fraction, Y):
+    """The single-launch fused IB+LB step (default) and the four-kernel chain (IBLB_FLAG_NO_FUSE)
+    run the same device functions in the same order: bit-identical state, with and without
+    CUDA-graph batches."""
+    X = c_num * c_space
+    kw = dict(c_num=c_num, c_space=c_space, c_fraction=c_fraction)
+    a = Solver(Params.channel(X, Y, **kw))
+    b = Solver(Params.channel(X, Y, flags=FLAG_NO_FUSE | FLAG_NO_GRAPH, **kw))
+    c = Solver(Params.channel(X, Y, flags=FLAG_NO_GRAPH, **kw))
+    for n in (1, 2, 17, 9):
+        for s in (a, b, c):
+            s.step(n)
+        assert a.last_step_launches <= n + n // 8 + 1  # one launch per iteration (+ batch ends)
+        assert b.last_step_launches == 4 * n
+        ref = (b.fields(), b.markers(), b.force(), b.populations())
+        for s in (a, c):
+            got = (s.fields(), s.markers(), s.force(), s.populations())
+            for x, y in zip(ref[0] + ref[1] + ref[2:], got[0] + got[1] + got[2:]):
+                assert np.array_equal(x, y)
+            assert s.Q == b.Q and s.it == b.it
+    for s in (a, b, c):
+        s.close()
 
 
 def test_results_are_run_to_run_deterministic():

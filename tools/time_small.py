@@ -1,0 +1,38 @@
+"""Development timing (GPU box): per-step time of the cilia cases, fused single-launch step vs the
+four-kernel chain vs pure LB on the same grid.  IB share = (t_ib_run - t_pure_lb) / t_ib_run."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from cuda_iblb_11_b200 import FLAG_NO_FUSE, FLAG_NO_GRAPH, Params, Solver
+
+
+def t_step(p, n, warm):
+    s = Solver(p)
+    s.step(warm)
+    s.sync()
+    best = 1e9
+    for _ in range(3):
+        s.step(n)
+        s.sync()
+        best = min(best, s.last_step_seconds / n)
+    s.close()
+    return best * 1e6
+
+
+if __name__ == "__main__":
+    cases = [(288, 192, 6, 48, 4000), (576, 192, 12, 48, 4000), (2304, 192, 48, 48, 2000),
+             (8192, 192, 64, 128, 1000), (8192, 2048, 64, 128, 200), (8192, 8192, 64, 128, 40)]
+    if len(sys.argv) > 1:
+        cases = cases[:int(sys.argv[1])]
+    for (X, Y, cn, cs, n) in cases:
+        kw = dict(c_num=cn, c_space=cs, c_fraction=cn)
+        fused = t_step(Params.channel(X, Y, **kw), n, 50)
+        fused_direct = t_step(Params.channel(X, Y, flags=FLAG_NO_GRAPH, **kw), n, 50)
+        chain = t_step(Params.channel(X, Y, flags=FLAG_NO_FUSE, **kw), n, 50)
+        lb = t_step(Params.channel(X, Y, gx=1e-7), n, 50)
+        print("%5dx%-5d %3d cilia: fused %.2f us (direct launches %.2f), 4-kernel chain %.2f, "
+              "pure LB %.2f us/step | %.0f MLUPS | IB share fused %.1f%% chain %.1f%%" % (
+                  X, Y, cn, fused, fused_direct, chain, lb, X * Y / fused,
+                  100 * (fused - lb) / fused, 100 * (chain - lb) / chain), flush=True)
