@@ -27,18 +27,22 @@ __device__ __forceinline__ int beat_phase(int it, int m, int p_step, int T) {
     return (it + m * p_step == T) ? T : (it + m * p_step) % T;
 }
 
-// main.cu:137-145 for one marker; cs[n-1] = (cos, sin)(n*2*PI*phase/T)
+// main.cu:137-145 for one marker; cs[n-1] = (cos, sin)(n*2*PI*phase/T).  Explicit intrinsics: the
+// same bits in every kernel that inlines it (see lb_device.cuh).
 __device__ __forceinline__ float2 marker_pos(const float *cf, const double2 *cs, float offset) {
-    float sx = 1. * 111 * cf[0] * 0.5 + offset;
-    float sy = 1. * 111 * cf[1] * 0.5;
+    float sx = __dadd_rn(__dmul_rn(__dmul_rn(111., (double)cf[0]), 0.5), (double)offset);
+    float sy = __dmul_rn(__dmul_rn(111., (double)cf[1]), 0.5);
 #pragma unroll
     for (int n = 1; n < 7; n++) {
-        sx += 1. * 111 * (cf[2 * n + 0] * cs[n - 1].x + cf[14 + 2 * n + 0] * cs[n - 1].y);
-        sy += 1. * 111 * (cf[2 * n + 1] * cs[n - 1].x + cf[14 + 2 * n + 1] * cs[n - 1].y);
+        const double tx = __fma_rn((double)cf[2 * n + 0], cs[n - 1].x,
+                                   __dmul_rn((double)cf[14 + 2 * n + 0], cs[n - 1].y));
+        const double ty = __fma_rn((double)cf[2 * n + 1], cs[n - 1].x,
+                                   __dmul_rn((double)cf[14 + 2 * n + 1], cs[n - 1].y));
+        sx = __dadd_rn((double)sx, __dmul_rn(111., tx));
+        sy = __dadd_rn((double)sy, __dmul_rn(111., ty));
     }
     return make_float2(sx, sy);
 }
-
 
 // trig table of one cilium at iteration `it`: t in [0,12): n = t/2+1, even t -> cos, odd -> sin of
 // n*2*PI*phase/T evaluated left to right in double as main.cu:143-144
@@ -70,20 +74,19 @@ __device__ __forceinline__ void marker_state(const float *cf, const double2 *cs0
 }
 
 // one factor of the 3-point delta, ImmersedBoundary.cu:21-81 (truncated prefactors, float |r|,
-// double body, float result)
+// double body, float result); explicit intrinsics for kernel-independent bits
 __device__ __forceinline__ float delta_1d(float r) {
-    double a = 0., b = 0., d = 0.;
-    int c = 0;
-    if (r <= 1.5) {
-        if (r <= 0.5) {
-            a = 0.33333; b = 1.; c = 1; d = r;
-        } else {
-            a = 0.16667; b = 5. - 3. * r; c = -1; d = 1 - r;
-        }
+    if (!(r <= 1.5)) return 0.f;
+    const double rd = r;
+    if (r <= 0.5) {  // 0.33333 * (1 + sqrt(1 - 3 r^2))
+        const double q = sqrt(__fma_rn(__dmul_rn(-3., rd), rd, 1.));
+        return __dmul_rn(0.33333, __dadd_rn(1., q));
     }
-    return a * (b + c * sqrt(-3. * d * d + 1));
+    // 0.16667 * (5 - 3 r - sqrt(1 - 3 (1 - r)^2))
+    const double d = 1 - r;  // float subtraction, as ImmersedBoundary.cu:46 (`d = 1-dx`)
+    const double q = sqrt(__fma_rn(__dmul_rn(-3., d), d, 1.));
+    return __dmul_rn(0.16667, __dsub_rn(__fma_rn(-3., rd, 5.), q));
 }
-
 
 // Term i (0..8) of the interpolation sum of marker (sm, us): 2*delta*rho*(u_s - u) at support node
 // i (ImmersedBoundary.cu:117-128), with rho and u of that node built from the nine populations it

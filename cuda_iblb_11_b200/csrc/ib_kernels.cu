@@ -36,85 +36,119 @@ __global__ void ib_coef(const int *k_of_j, float *coef) {
         }
 }
 
-// One block (128 threads) per cilium: positions at `it` and `it-1`, velocity, wrap, bbox.
-__global__ void __launch_bounds__(128) ib_kinematics(const IbParams p) {
-    __shared__ __align__(16) double trig[24];  // [t][n][cos,sin]: t=0 current, t=1 previous
+// Everything about the markers that does not depend on the fluid, for a BATCH of iterations in one
+// launch (the cilia are prescribed: main.cu:77-252 is a function of `it` alone): grid =
+// (c_num, iterations), one block per cilium and iteration.
+//   1. kinematics (main.cu:77-173,193-209) of the cilium and of the r_max-1 cilia to its left;
+//   2. epsilon (main.cu:217-248): own markers against the left neighbours' markers;
+//   3. the spreading stencil of every marker (columns/rows within 1.5 and their delta factors) and
+//      the cilium's bounding box.
+// Slot b of the marker arrays (stride Ns) receives iteration it0 + b.  Replaces the reference's
+// define_filament and boundary_check launches, off the fluid's critical path: one launch per
+// kKinBatch iterations.
+__global__ void __launch_bounds__(1024) ib_kinematics_batch(const IbParams p) {
+    __shared__ __align__(16) double trig[kMaxLeftCilia][24];  // slot 0 = own, e = cilium m-e
+    __shared__ float2 pos[kMaxLeftCilia][kMarkersPerCilium];
+    __shared__ float2 vel[kMarkersPerCilium];
+    __shared__ int closef[kMarkersPerCilium];
+    __shared__ float wgt[kMarkersPerCilium][8];
     __shared__ float red_min[4], red_max[4];
-    const int m = blockIdx.x;
-    const int t = threadIdx.x;
-    const int T = p.T;
-    const int it = p.it_ptr ? *p.it_ptr : p.it;
-    if (t < 24) trig[t] = beat_trig(t % 12, it - t / 12, m, p.p_step, T);  // main.cu:143
+    const int m = blockIdx.x, slot = blockIdx.y;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int it = (p.it_ptr ? *p.it_ptr : p.it) + p.it_off + slot;
+    const int r_max = p.r_max < 1 ? 1 : p.r_max;  // cilia whose positions are needed
+    if (t < kMarkersPerCilium) closef[t] = 0;
+    for (int idx = t; idx < r_max * 24; idx += 1024) {
+        const int e = idx / 24, r = idx - e * 24;
+        const int mm = (m - e < 0) ? (m - e + p.c_num) : (m - e);
+        if (e == 0 || r < 12) trig[e][r] = beat_trig(r % 12, it - r / 12, mm, p.p_step, p.T);
+    }
     __syncthreads();
-    float sx = 0.f;
-    if (t < kMarkersPerCilium) {
+    for (int idx = t; idx < r_max * kMarkersPerCilium; idx += 1024) {
+        const int e = idx / kMarkersPerCilium, j = idx - e * kMarkersPerCilium;
+        const int mm = (m - e < 0) ? (m - e + p.c_num) : (m - e);
         float2 sm, v;
-        marker_state(p.coef + t * 28, reinterpret_cast<const double2 *>(trig),
-                     reinterpret_cast<const double2 *>(trig + 12), m, it, p.c_space, p.c_num,
-                     p.L.XDIM, sm, v);
-        sx = sm.x;
-        const int k = m * kMarkersPerCilium + t;
+        // neighbours only need the position: their trig[e][12..23] is not filled, it = 0 skips it
+        marker_state(p.coef + j * 28, reinterpret_cast<const double2 *>(trig[e]),
+                     reinterpret_cast<const double2 *>(trig[e] + 12), mm, e == 0 ? it : 0,
+                     p.c_space, p.c_num, p.L.XDIM, sm, v);
+        pos[e][j] = sm;
+        if (e == 0) vel[j] = v;
+    }
+    __syncthreads();
+    // ---- epsilon: any marker of the r_max-1 cilia to the left within 1 unit on both axes ----
+    {
+        const int j = t % kMarkersPerCilium, part = t / kMarkersPerCilium;  // 10 scanners a marker
+        if (part < 10) {
+            const float2 sm = pos[0][j];
+            bool close = false;
+            for (int idx = part; idx < (r_max - 1) * kMarkersPerCilium; idx += 10) {
+                const float2 o = (&pos[1][0])[idx];
+                close |= (fabsf(o.x - sm.x) < 1) && (fabsf(o.y - sm.y) < 1);
+            }
+            if (close) closef[j] = 1;
+        }
+    }
+    // ---- spreading stencil: columns bx..bx+3, rows by..by+3 and their 1-D delta factors ----
+    if (t < kMarkersPerCilium * 8) {
+        const int j = t >> 3, i = t & 7;
+        const float2 sm = pos[0][j];
+        const int bx = (int)ceilf(sm.x - 1.5f), by = (int)ceilf(sm.y - 1.5f);
+        wgt[j][i] = (i < 4) ? delta_1d(fabsf((bx + i) - sm.x)) : delta_1d(fabsf((by + i - 4) - sm.y));
+    }
+    __syncthreads();
+    if (t < kMarkersPerCilium) {
+        const long long k = (long long)slot * p.Ns + m * kMarkersPerCilium + t;
+        const float2 sm = pos[0][t];
         p.M.s[k] = sm;
-        p.M.u_s[k] = v;
+        p.M.u_s[k] = vel[t];
+        p.M.eps[k] = closef[t] ? 0 : 1;
+        p.M.wx[k] = make_float4(wgt[t][0], wgt[t][1], wgt[t][2], wgt[t][3]);
+        p.M.wy[k] = make_float4(wgt[t][4], wgt[t][5], wgt[t][6], wgt[t][7]);
+        p.M.base[k] = make_int2((int)ceilf(sm.x - 1.5f), (int)ceilf(sm.y - 1.5f));
     }
     // bbox of the wrapped x positions (for the spreading tiles)
-    float lo = (t < kMarkersPerCilium) ? sx : 3.0e38f, hi = (t < kMarkersPerCilium) ? sx : -3.0e38f;
+    if (t < 128) {
+        const float sx = (t < kMarkersPerCilium) ? pos[0][t].x : 0.f;
+        float lo = (t < kMarkersPerCilium) ? sx : 3.0e38f, hi = (t < kMarkersPerCilium) ? sx : -3.0e38f;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
-        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
-    }
-    if ((t & 31) == 0) {
-        red_min[t >> 5] = lo;
-        red_max[t >> 5] = hi;
+        for (int o = 16; o > 0; o >>= 1) {
+            lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+            hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+        }
+        if (lane == 0) {
+            red_min[warp] = lo;
+            red_max[warp] = hi;
+        }
     }
     __syncthreads();
     if (t == 0)
-        p.M.bbox[m] = make_float2(fminf(fminf(red_min[0], red_min[1]), red_min[2]),
-                                  fmaxf(fmaxf(red_max[0], red_max[1]), red_max[2]));
+        p.M.bbox[slot * p.c_num + m] =
+            make_float2(fminf(fminf(red_min[0], red_min[1]), red_min[2]),
+                        fmaxf(fmaxf(red_max[0], red_max[1]), red_max[2]));
 }
 
-// Warp per marker: epsilon (main.cu:217-248), then F_s (ImmersedBoundary.cu:94-133) with the
-// macroscopic values of the nine support nodes built from pulled populations
-// (LatticeBoltzmann.cu:173-373 pull form + :396-405).
-__global__ void __launch_bounds__(256) ib_interpolate(const IbParams p) {
-    const int lane = threadIdx.x & 31;
-    const int k = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-    if (k >= p.Ns) return;
-    const Lattice &L = p.L;
-    const float2 sm = p.M.s[k];
-    const float2 us = p.M.u_s[k];
-
-    // ---- epsilon: any marker of the r_max-1 cilia to the left within 1 unit on both axes ----
-    const int m = k / kMarkersPerCilium;
-    bool close = false;
-    for (int r = 1; r < p.r_max; r++) {
-        const int mm = (m - r < 0) ? (m - r + p.c_num) : (m - r);
-        for (int l = lane; l < kMarkersPerCilium; l += 32) {
-            const float2 o = p.M.s[l + mm * kMarkersPerCilium];
-            close |= (fabsf(o.x - sm.x) < 1) && (fabsf(o.y - sm.y) < 1);
-        }
-    }
-    const int eps = __any_sync(0xffffffffu, close) ? 0 : 1;
-
-    // ---- lanes 0..8: support node i of the marker ----
+// F_s of every marker (ImmersedBoundary.cu:94-133), the only per-marker work that needs the fluid:
+// nine lanes per marker (one per support node, each pulling the node's nine populations), three
+// markers per warp, 24 per block so that the markers spread over all SMs; the float accumulation in
+// the fixed order i = 0..8 (Q6) runs over warp shuffles.  `p.M` points at the iteration's slot.
+__global__ void __launch_bounds__(256) ib_interp(const IbParams p) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane / 9, i9 = lane - 9 * g;
+    const int k = (blockIdx.x * 8 + warp) * 3 + g;
+    const bool on = lane < 27 && k < p.Ns;
     double tx = 0., ty = 0.;
-    if (lane < 9) interp_term(L, p.src, sm, us, lane, tx, ty);
-    // F_s is a float re-rounded after each of the nine terms, fixed order (Q6)
+    if (on) interp_term(p.L, p.src, p.M.s[k], p.M.u_s[k], i9, tx, ty);
     float Fx = 0.f, Fy = 0.f;
 #pragma unroll
-    for (int i = 0; i < 9; i++) {
-        const double ax = __shfl_sync(0xffffffffu, tx, i);
-        const double ay = __shfl_sync(0xffffffffu, ty, i);
+    for (int i = 0; i < 9; i++) {  // float re-rounded after each term, fixed order (Q6)
+        const int srcl = lane < 27 ? g * 9 + i : lane;
+        const double ax = __shfl_sync(0xffffffffu, tx, srcl);
+        const double ay = __shfl_sync(0xffffffffu, ty, srcl);
         Fx += ax;
         Fy += ay;
     }
-    if (lane == 0) {
-        p.M.F_s[k] = make_float2(Fx, Fy);
-        p.M.eps[k] = eps;
-        // graph mode: the kinematics of this step have read the counter (previous kernel)
-        if (k == 0 && p.it_ptr) *p.it_ptr = *p.it_ptr + 1;
-    }
+    if (on && i9 == 0) p.M.F_s[k] = make_float2(Fx, Fy);
 }
 
 // CTA per 8x32-node tile of the band: force = sum over markers (ascending) of

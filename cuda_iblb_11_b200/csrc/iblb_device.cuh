@@ -21,6 +21,8 @@ constexpr double kCs = 0.57735;  // device sound speed, LatticeBoltzmann.cu:11 (
 constexpr int kMarkersPerCilium = 96;   // main.cu:83
 constexpr int kFinePoints = 9600;       // main.cu:81
 constexpr int kSpreadTileX = 8, kSpreadTileY = 32;
+constexpr int kKinBatch = 8;       // iterations of marker kinematics computed per launch
+constexpr int kMaxLeftCilia = 16;  // r_max = 2*96/c_space (main.cu:185) must not exceed this
 
 struct Lattice {
     int W;          // owned columns
@@ -58,12 +60,18 @@ struct LbParams {
     // columns this launch covers: c in [0, col_count) -> x = col_begin + c, and x += split_skip
     // when x >= split_at (boundary launch = the first and last G columns in one grid)
     int col_begin, col_count, split_at, split_skip;
+    int row_begin;  // first row this launch covers (multiple of 64; lb_fused_v2 only)
 };
 
 struct MarkerArrays {
     float2 *s, *u_s, *F_s;   // position, velocity, force per marker
     int *eps;                // on/off switch
     float2 *bbox;            // per cilium (min x, max x) of the wrapped positions
+    // spreading stencil of each marker: the (up to) four columns bx..bx+3 and rows by..by+3 within
+    // 1.5 of it and their 1-D delta factors (0 beyond the reach), so that the per-node loops of
+    // the spreading only multiply two table entries
+    float4 *wx, *wy;
+    int2 *base;
 };
 
 struct IbParams {
@@ -71,27 +79,25 @@ struct IbParams {
     const double *src;       // populations the step pulls from
     MarkerArrays M;
     const float *coef;       // [96][28] a_n(x,y), b_n(x,y), n = 0..6 per marker (main.cu:109-135)
-    int c_num, c_space, T, p_step, it;
-    int *it_ptr;             // when set, the iteration number lives on the device (CUDA graphs)
+    int c_num, c_space, T, p_step;
+    int it, it_off;          // iteration = (it_ptr ? *it_ptr : it) + it_off
+    const int *it_ptr;       // when set, the iteration number lives on the device (CUDA graphs)
     int Ns;
     int r_max;               // main.cu:185
     double *band;            // force band, see LbParams
     int band_rows, band_ld;
 };
 
-// fused IB+LB step (fused_step.cu)
-constexpr int kFusedMaxCilia = 16;  // cilia whose marker states one band tile may need
-constexpr int kFusedMaxList = 512;  // markers whose support can touch one 8x64 tile
+// LB step with fused spreading (fused_step.cu)
+constexpr int kBandMaxRel = 128;   // cilia whose bounding box may overlap one 8-column tile
+constexpr int kBandMaxList = 512;  // markers whose support can touch one 8x64 tile
 
-struct FusedParams {
+struct BandParams {
     LbParams lb;
-    const float *coef;       // as IbParams::coef
-    int c_num, c_space, T, p_step, r_max;
-    int it, it_off;          // iteration = (it_ptr ? *it_ptr : it) + it_off
-    const int *it_ptr;
-    float reach;             // bound on |marker x - translated base of its cilium| (from coef)
+    MarkerArrays M;
+    int c_num;
     int band_rows;           // rows that can receive IB force (multiple of 64)
-    int *err;                // set non-zero when a tile exceeds kFusedMaxCilia / kFusedMaxList
+    int *err;                // set non-zero when a tile exceeds kBandMaxRel / kBandMaxList
 };
 
 }  // namespace iblb

@@ -27,10 +27,10 @@ __global__ void halo_push(const Lattice L, const double *buf, Remote left, Remot
 __global__ void lb_moments(const LbParams p, int streamed, double *rho_out, double *u_out,
                            double *f_out, double *force_out);
 __global__ void ib_coef(const int *k_of_j, float *coef);
-__global__ void ib_kinematics(const IbParams p);
-__global__ void ib_interpolate(const IbParams p);
+__global__ void ib_kinematics_batch(const IbParams p);
+__global__ void ib_interp(const IbParams p);
 __global__ void ib_spread(const IbParams p);
-__global__ void iblb_fused_step(const FusedParams p);
+__global__ void lb_band_step(const BandParams p);
 __global__ void it_advance(int *it_ptr, int by);
 __global__ void slab_wait(const volatile int *flag_l, const volatile int *flag_r, int need);
 __global__ void slab_signal(int *left_flag, int *right_flag, int value);
@@ -54,12 +54,12 @@ struct iblb_solver {
     double *band;
     int band_rows, band_ld;
     int *it_dev;               // device copy of `it` read by the graph-captured kinematics
-    // fused IB+LB step (single launch per iteration)
-    bool fuse_ok;              // geometry allows it (whole channel, YDIM % 64 == 0, reach bounds)
-    bool ib_stale;             // marker arrays / force band not materialised for the last step
+    long long kin_base;        // marker slots hold iterations [kin_base, kin_base + kKinBatch); -1: none
+    // two-launch iteration: ib_markers + lb_band_step (spreading fused into the LB kernel)
+    bool fuse_ok;              // geometry allows it (whole channel, YDIM % 64 == 0)
+    bool ib_stale;             // force band not materialised for the last step
     float reach_x, reach_y;    // bounds on the marker excursion from the cilium base
     int *err_dev;
-    cudaGraphExec_t fused_graph;  // kFusedBatch iterations + it_advance
     // flux
     double *qacc, *qpart;
     int nq;
@@ -69,7 +69,8 @@ struct iblb_solver {
     cudaStream_t stream;
     cudaEvent_t ev0, ev1;
     bool timed;
-    cudaGraphExec_t graph_exec;  // two iterations (A->B, B->A), built lazily
+    cudaGraphExec_t graph_exec;  // a batch of iterations + it_advance, built lazily
+    unsigned long long graph_launches;  // kernel nodes in it
     unsigned long long last_launches;
     // slab coupling
     bool connected;

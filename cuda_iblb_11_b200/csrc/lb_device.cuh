@@ -25,24 +25,32 @@ __device__ __forceinline__ double2 ldg2(const double *p) {
     return __ldg(reinterpret_cast<const double2 *>(p));
 }
 
+// The arithmetic below is written with explicit round-to-nearest intrinsics so that every kernel
+// that inlines it (lb_fused_v1/v2, the fused IB+LB step, the band kernel) produces the same bits:
+// left to the compiler, which product is contracted into which sum depends on the inlining context.
+#define DM(a, b) __dmul_rn((a), (b))
+#define DA(a, b) __dadd_rn((a), (b))
+#define DS(a, b) __dsub_rn((a), (b))
+#define DF(a, b, c) __fma_rn((a), (b), (c))
+
 // TRT relaxation of one antiparallel pair (a = +c, b = -c) plus the Guo term.
 // LatticeBoltzmann.cu:88-134 with f0 split into its even/odd parts analytically.
 __device__ __forceinline__ void relax_pair(double &fa, double &fb, double rw, double cu,
                                            double base, double wp, double wm, double kw,
                                            double cF, double uF, bool forced) {
-    const double f0p = rw * (base + cu * cu * kIcs4h);
-    const double f0m = rw * (cu * kIcs2);
-    const double fp = 0.5 * (fa + fb);
-    const double fm = 0.5 * (fa - fb);
-    const double A = wp * (fp - f0p);
-    const double B = wm * (fm - f0m);
-    double na = fa - A - B;
-    double nb = fb - A + B;
+    const double f0p = DM(rw, DF(DM(cu, cu), kIcs4h, base));
+    const double f0m = DM(rw, DM(cu, kIcs2));
+    const double fp = DM(0.5, DA(fa, fb));
+    const double fm = DM(0.5, DS(fa, fb));
+    const double dp = DS(fp, f0p);
+    const double dm = DS(fm, f0m);
+    double na = DF(-wm, dm, DF(-wp, dp, fa));
+    double nb = DF(wm, dm, DF(-wp, dp, fb));
     if (forced) {
-        const double S = kw * (cu * cF * kIcs4 - uF * kIcs2);
-        const double D = kw * (cF * kIcs2);
-        na += S + D;
-        nb += S - D;
+        const double S = DM(kw, DF(-uF, kIcs2, DM(DM(cu, cF), kIcs4)));
+        const double D = DM(kw, DM(cF, kIcs2));
+        na = DA(na, DA(S, D));
+        nb = DA(nb, DS(S, D));
     }
     fa = na;
     fb = nb;
@@ -52,23 +60,23 @@ __device__ __forceinline__ void relax_pair(double &fa, double &fb, double rw, do
 // (ImmersedBoundary.cu:249-255), then equilibrium + forcing + TRT.  Returns u_x.
 __device__ __forceinline__ double collide_node(double (&f)[9], double Fx, double Fy, bool forced,
                                                const LbParams &p) {
-    const double rho = f[0] + f[1] + f[2] + f[3] + f[4] + f[5] + f[6] + f[7] + f[8];
-    const double mx = f[1] - f[3] + f[5] - f[6] - f[7] + f[8];
-    const double my = f[2] - f[4] + f[5] + f[6] - f[7] - f[8];
-    const double ir = 1.0 / rho;
-    const double ux = (mx + p.half * Fx) * ir;
-    const double uy = (my + p.half * Fy) * ir;
-    const double base = 1.0 - (ux * ux + uy * uy) * kIcs2h;
+    const double rho = DA(DA(DA(DA(DA(DA(DA(DA(f[0], f[1]), f[2]), f[3]), f[4]), f[5]), f[6]), f[7]), f[8]);
+    const double mx = DA(DS(DS(DA(DS(f[1], f[3]), f[5]), f[6]), f[7]), f[8]);
+    const double my = DS(DS(DA(DA(DS(f[2], f[4]), f[5]), f[6]), f[7]), f[8]);
+    const double ir = __drcp_rn(rho);
+    const double ux = DM(DF(p.half, Fx, mx), ir);
+    const double uy = DM(DF(p.half, Fy, my), ir);
+    const double base = DF(-DF(uy, uy, DM(ux, ux)), kIcs2h, 1.0);
     const double wp = p.omega_plus, wm = p.omega_minus;
-    const double uF = ux * Fx + uy * Fy;
-    const double k1 = p.kforce * kW1, k2 = p.kforce * kW2;
-    const double r1 = rho * kW1, r2 = rho * kW2;
+    const double uF = DF(uy, Fy, DM(ux, Fx));
+    const double k1 = DM(p.kforce, kW1), k2 = DM(p.kforce, kW2);
+    const double r1 = DM(rho, kW1), r2 = DM(rho, kW2);
     // rest population: no force term (LatticeBoltzmann.cu:86)
-    f[0] = f[0] - wp * (f[0] - rho * kW0 * base);
+    f[0] = DF(-wp, DS(f[0], DM(DM(rho, kW0), base)), f[0]);
     relax_pair(f[1], f[3], r1, ux, base, wp, wm, k1, Fx, uF, forced);
     relax_pair(f[2], f[4], r1, uy, base, wp, wm, k1, Fy, uF, forced);
-    relax_pair(f[5], f[7], r2, ux + uy, base, wp, wm, k2, Fx + Fy, uF, forced);
-    relax_pair(f[6], f[8], r2, uy - ux, base, wp, wm, k2, Fy - Fx, uF, forced);
+    relax_pair(f[5], f[7], r2, DA(ux, uy), base, wp, wm, k2, DA(Fx, Fy), uF, forced);
+    relax_pair(f[6], f[8], r2, DS(uy, ux), base, wp, wm, k2, DS(Fy, Fx), uF, forced);
     return ux;
 }
 

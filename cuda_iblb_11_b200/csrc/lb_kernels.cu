@@ -25,56 +25,18 @@ namespace iblb {
 // Fast path: YDIM % 64 == 0.  grid = ceil(W*YDIM/2 / 256), block = 256.
 __global__ void __launch_bounds__(256, 3) lb_fused_v2(const LbParams p) {
     const Lattice &L = p.L;
-    const int HP = L.YDIM >> 1;  // row pairs per column (multiple of 32: warps never straddle)
+    const int HP = (L.YDIM - p.row_begin) >> 1;  // row pairs per column (multiple of 32)
     const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (gid >= (long long)p.col_count * HP) return;  // whole warps only
     const int c = (int)(gid / HP);
     const int yp = (int)(gid - (long long)c * HP);
     int x = p.col_begin + c;
     if (x >= p.split_at) x += p.split_skip;
-    const int y0 = yp << 1;
+    const int y0 = p.row_begin + (yp << 1);
     const int lane = threadIdx.x & 31;
-    const bool at_bottom = (y0 == 0);
-    const bool at_top = (y0 + 2 == L.YDIM);
 
-    const double *__restrict__ src = p.src;
-    const long long P = L.plane;
-    const long long cm = L.off(x - 1, y0), c0 = L.off(x, y0), cp = L.off(x + 1, y0);
-
-    // ---- all loads first: 9 aligned 128-bit loads per thread ----
-    const double2 v0 = ldg2(src + 0 * P + c0);
-    const double2 v1 = ldg2(src + 1 * P + cm);  // c = (+1, 0): from x-1
-    const double2 v2 = ldg2(src + 2 * P + c0);  // c = ( 0,+1): from y-1
-    const double2 v3 = ldg2(src + 3 * P + cp);  // c = (-1, 0): from x+1
-    const double2 v4 = ldg2(src + 4 * P + c0);  // c = ( 0,-1): from y+1
-    const double2 v5 = ldg2(src + 5 * P + cm);  // c = (+1,+1)
-    const double2 v6 = ldg2(src + 6 * P + cp);  // c = (-1,+1)
-    const double2 v7 = ldg2(src + 7 * P + cp);  // c = (-1,-1)
-    const double2 v8 = ldg2(src + 8 * P + cm);  // c = (+1,-1)
-    // edge values for the row below lane 0 / above lane 31 (walls folded in)
-    double e2 = 0., e5 = 0., e6 = 0., e4 = 0., e7 = 0., e8 = 0.;
-    if (lane == 0) {
-        if (at_bottom) {
-            e2 = v4.x;  // f2(x,0) <- f4(x,0): already loaded (same column, row y0)
-            e5 = __ldg(src + 7 * P + c0);
-            e6 = __ldg(src + 8 * P + c0);
-        } else {
-            e2 = __ldg(src + 2 * P + c0 - 1);
-            e5 = __ldg(src + 5 * P + cm - 1);
-            e6 = __ldg(src + 6 * P + cp - 1);
-        }
-    }
-    if (lane == 31) {
-        if (at_top) {
-            e4 = v2.y;  // f4(x,Y-1) <- f2(x,Y-1)
-            e7 = __ldg(src + 6 * P + c0 + 1);
-            e8 = __ldg(src + 5 * P + c0 + 1);
-        } else {
-            e4 = __ldg(src + 4 * P + c0 + 2);
-            e7 = __ldg(src + 7 * P + cp + 2);
-            e8 = __ldg(src + 8 * P + cm + 2);
-        }
-    }
+    Pulled q;
+    load_pulled(L, p.src, x, y0, lane, q);
     // force: IB band (rows < band_rows) + uniform body force
     double Fx0 = p.gx, Fy0 = p.gy, Fx1 = p.gx, Fy1 = p.gy;
     bool forced = (p.gx != 0.0) | (p.gy != 0.0);
@@ -86,49 +48,19 @@ __global__ void __launch_bounds__(256, 3) lb_fused_v2(const LbParams p) {
         forced = true;
     }
 
-    // ---- shift the six populations with c_y != 0 by one row in registers ----
     double a[9], b[9];  // node y0, node y0+1
-    a[0] = v0.x; b[0] = v0.y;
-    a[1] = v1.x; b[1] = v1.y;
-    a[3] = v3.x; b[3] = v3.y;
-    {
-        double t;
-        t = shfl_up1(v2.y); a[2] = lane == 0 ? e2 : t; b[2] = v2.x;
-        t = shfl_up1(v5.y); a[5] = lane == 0 ? e5 : t; b[5] = v5.x;
-        t = shfl_up1(v6.y); a[6] = lane == 0 ? e6 : t; b[6] = v6.x;
-        t = shfl_dn1(v4.x); a[4] = v4.y; b[4] = lane == 31 ? e4 : t;
-        t = shfl_dn1(v7.x); a[7] = v7.y; b[7] = lane == 31 ? e7 : t;
-        t = shfl_dn1(v8.x); a[8] = v8.y; b[8] = lane == 31 ? e8 : t;
-    }
-
+    shift_pulled(q, lane, a, b);
     const double ux0 = collide_node(a, Fx0, Fy0, forced, p);
     const double ux1 = collide_node(b, Fx1, Fy1, forced, p);
-
-    // ---- 9 aligned 128-bit stores ----
-    double *__restrict__ dst = p.dst;
-#pragma unroll
-    for (int i = 0; i < 9; i++)
-        *reinterpret_cast<double2 *>(dst + i * P + c0) = make_double2(a[i], b[i]);
-
-    // boundary columns: second copy into the neighbours' ghost columns (block-uniform per warp)
-    if (x < p.left.G) {
-#pragma unroll
-        for (int i = 0; i < 9; i++)
-            store_remote2(p.left, p.left.W + x, y0, i, make_double2(a[i], b[i]));
-    }
-    if (x >= L.W - p.right.G) {
-#pragma unroll
-        for (int i = 0; i < 9; i++)
-            store_remote2(p.right, x - L.W, y0, i, make_double2(a[i], b[i]));
-    }
+    store_pair(p, x, y0, a, b);
 
     // flux through the plane x = XDIM-5 (ImmersedBoundary.cu:259-264): fixed-order warp tree,
-    // one running sum per warp slot, summed on the host in slot order => deterministic
+    // one running sum per 64-row slot, summed on the host in slot order => deterministic
     if (x == p.xq && p.qacc != nullptr) {
-        double q = ux0 + ux1;
+        double s = ux0 + ux1;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) q += __shfl_down_sync(0xffffffffu, q, o);
-        if (lane == 0) p.qacc[yp >> 5] += q / (double)L.YDIM;
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+        if (lane == 0) p.qacc[y0 >> 6] += s / (double)L.YDIM;
     }
 }
 

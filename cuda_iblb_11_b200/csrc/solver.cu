@@ -58,21 +58,32 @@ LbParams make_lb_params(const iblb_solver *s, int src_idx) {
     q.col_count = s->L.W;
     q.split_at = 1 << 30;
     q.split_skip = 0;
+    q.row_begin = 0;
     return q;
 }
 
-IbParams make_ib_params(const iblb_solver *s, int src_idx) {
+// marker arrays of iteration slot `slot` (F_s has a single slot)
+MarkerArrays marker_slot(const iblb_solver *s, int slot) {
+    MarkerArrays m = s->M;
+    const size_t o = (size_t)slot * s->Ns;
+    m.s += o; m.u_s += o; m.eps += o; m.wx += o; m.wy += o; m.base += o;
+    m.bbox += (size_t)slot * s->p.c_num;
+    return m;
+}
+
+IbParams make_ib_params(const iblb_solver *s, int src_idx, int slot) {
     IbParams q;
     memset(&q, 0, sizeof q);
     q.L = s->L;
     q.src = s->buf[src_idx];
-    q.M = s->M;
+    q.M = marker_slot(s, slot);
     q.coef = s->coef;
     q.c_num = (int)s->p.c_num;
     q.c_space = (int)s->p.c_space;
     q.T = (int)s->p.T;
     q.p_step = s->p.p_step;
     q.it = (int)s->it;
+    q.it_off = 0;
     q.it_ptr = nullptr;
     q.Ns = s->Ns;
     q.r_max = (int)(2 * kMarkersPerCilium / (double)s->p.c_space);  // main.cu:185
@@ -101,6 +112,7 @@ static int init_state(iblb_solver *s, const double *rho_dev, const double *u_dev
     if (s->it_dev) IBLB_CUDA(cudaMemsetAsync(s->it_dev, 0, sizeof(int), s->stream));
     s->cur = 0;
     s->ib_stale = false;
+    s->kin_base = -1;
     s->flag_base += (int)s->it;  // all slabs reset together: later flag values stay above old ones
     s->it = 0;
     IBLB_CUDA(cudaStreamSynchronize(s->stream));
@@ -120,8 +132,10 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
         set_error("iblb_create: XDIM, YDIM must be >= 4 and YDIM even");
         return IBLB_EINVAL;
     }
-    if (p.c_num > 0 && (p.XDIM != p.c_num * p.c_space || p.c_num > 2048 || p.YDIM < 128)) {
-        set_error("iblb_create: with cilia XDIM must equal c_num*c_space, c_num <= 2048, YDIM >= 128");
+    if (p.c_num > 0 && (p.XDIM != p.c_num * p.c_space || p.c_num > 2048 || p.YDIM < 128 ||
+                        2 * kMarkersPerCilium / (int)p.c_space > kMaxLeftCilia)) {
+        set_error("iblb_create: with cilia XDIM must equal c_num*c_space, c_num <= 2048, "
+                  "YDIM >= 128, c_space >= 12");
         return IBLB_EINVAL;
     }
     if (!(p.TAU > 0.5) || !(p.TAU2 > 0.5)) {
@@ -176,21 +190,26 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
         s->band_rows = 128;
         s->band_ld = 128;
         TRY(cudaMalloc((void **)&s->band, sizeof(double) * 2 * (size_t)L.W * s->band_ld));
-        TRY(cudaMalloc((void **)&s->M.s, sizeof(float2) * s->Ns));
-        TRY(cudaMalloc((void **)&s->M.u_s, sizeof(float2) * s->Ns));
+        // marker arrays: kKinBatch iteration slots (stride Ns); F_s only for the current iteration
+        const size_t nm = (size_t)s->Ns * kKinBatch;
+        TRY(cudaMalloc((void **)&s->M.s, sizeof(float2) * nm));
+        TRY(cudaMalloc((void **)&s->M.u_s, sizeof(float2) * nm));
         TRY(cudaMalloc((void **)&s->M.F_s, sizeof(float2) * s->Ns));
-        TRY(cudaMalloc((void **)&s->M.eps, sizeof(int) * s->Ns));
-        TRY(cudaMalloc((void **)&s->M.bbox, sizeof(float2) * p.c_num));
+        TRY(cudaMalloc((void **)&s->M.eps, sizeof(int) * nm));
+        TRY(cudaMalloc((void **)&s->M.bbox, sizeof(float2) * p.c_num * kKinBatch));
+        TRY(cudaMalloc((void **)&s->M.wx, sizeof(float4) * nm));
+        TRY(cudaMalloc((void **)&s->M.wy, sizeof(float4) * nm));
+        TRY(cudaMalloc((void **)&s->M.base, sizeof(int2) * nm));
         TRY(cudaMalloc((void **)&s->coef, sizeof(float) * kMarkersPerCilium * 28));
         TRY(cudaMalloc((void **)&s->k_of_j_dev, sizeof(int) * kMarkersPerCilium));
         TRY(cudaMalloc((void **)&s->it_dev, sizeof(int)));
         TRY(cudaMalloc((void **)&s->err_dev, sizeof(int)));
         if (rc == IBLB_OK) TRY(cudaMemset(s->err_dev, 0, sizeof(int)));
         if (rc == IBLB_OK) {
-            TRY(cudaMemset(s->M.s, 0, sizeof(float2) * s->Ns));
-            TRY(cudaMemset(s->M.u_s, 0, sizeof(float2) * s->Ns));
+            TRY(cudaMemset(s->M.s, 0, sizeof(float2) * nm));
+            TRY(cudaMemset(s->M.u_s, 0, sizeof(float2) * nm));
             TRY(cudaMemset(s->M.F_s, 0, sizeof(float2) * s->Ns));
-            TRY(cudaMemset(s->M.eps, 0, sizeof(int) * s->Ns));
+            TRY(cudaMemset(s->M.eps, 0, sizeof(int) * nm));
             build_marker_table(s->k_of_j, (p.flags & IBLB_FLAG_PICK_HIGHEST_K) == 0);
             TRY(cudaMemcpy(s->k_of_j_dev, s->k_of_j.data(), sizeof(int) * kMarkersPerCilium,
                            cudaMemcpyHostToDevice));
@@ -229,14 +248,15 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
     const int xq = (int)p.XDIM - 5 - L.x0;
     s->xq_local = xq;
     s->flux_on = (p.c_num > 0 || (p.flags & IBLB_FLAG_HALF_FORCE_BODY)) && xq >= 0 && xq < L.W;
-    // single-launch fused IB+LB step: whole channel on this GPU, vector path, every tile's cilia
-    // set fits the kernel's shared-memory slots, markers stay inside the force band
+    // spreading fused into the LB kernel: whole channel on this GPU, vector path; in every mode the
+    // markers must stay inside the force band (rigorous bound from the coefficient table)
     if (p.c_num > 0) {
-        const int r_max = (int)(2 * kMarkersPerCilium / (double)p.c_space);
-        const int span = (int)((2. * s->reach_x + 11.) / p.c_space) + 2;
-        s->fuse_ok = !slab && s->vec2 && !(p.flags & IBLB_FLAG_NO_FUSE) &&
-                     (span + r_max - 1 <= kFusedMaxCilia || p.c_num <= (unsigned)kFusedMaxCilia) &&
-                     s->reach_y + 1.5f < (float)s->band_rows;
+        if (s->reach_y + 1.5f >= (float)s->band_rows) {
+            iblb_destroy(s);
+            set_error("iblb_create: cilia reach above the force band");
+            return IBLB_EINVAL;
+        }
+        s->fuse_ok = !slab && s->vec2 && !(p.flags & IBLB_FLAG_NO_FUSE);
     }
     // a lone solver is periodic with itself
     for (int b = 0; b < 2; b++) {
@@ -263,7 +283,6 @@ int iblb_destroy(iblb_solver *s) {
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
-    if (s->fused_graph) cudaGraphExecDestroy(s->fused_graph);
     cudaFree(s->err_dev);
     for (int f = 0; f < 2; f++) {
         for (int b = 0; b < 2; b++)
@@ -273,6 +292,7 @@ int iblb_destroy(iblb_solver *s) {
     cudaFree(s->buf[0]); cudaFree(s->buf[1]); cudaFree(s->qacc); cudaFree(s->qpart);
     cudaFree(s->flags); cudaFree(s->band); cudaFree(s->M.s); cudaFree(s->M.u_s);
     cudaFree(s->M.F_s); cudaFree(s->M.eps); cudaFree(s->M.bbox); cudaFree(s->coef);
+    cudaFree(s->M.wx); cudaFree(s->M.wy); cudaFree(s->M.base);
     cudaFree(s->k_of_j_dev); cudaFree(s->it_dev);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);

@@ -8,45 +8,31 @@
 
 namespace iblb {
 LbParams make_lb_params(const iblb_solver *s, int src_idx);
-IbParams make_ib_params(const iblb_solver *s, int src_idx);
+IbParams make_ib_params(const iblb_solver *s, int src_idx, int slot);
+MarkerArrays marker_slot(const iblb_solver *s, int slot);
 }  // namespace iblb
 using namespace iblb;
 
 namespace {
 
-constexpr unsigned kFusedBatch = 8;  // iterations per captured batch of the fused step (even)
+constexpr unsigned kGraphBatch = kKinBatch;  // iterations per captured batch (even: A/B swap back)
 
-FusedParams make_fused_params(const iblb_solver *s, int src_idx) {
-    FusedParams q;
+BandParams make_band_params(const iblb_solver *s, int src_idx, int slot) {
+    BandParams q;
     memset(&q, 0, sizeof q);
     q.lb = make_lb_params(s, src_idx);
     q.lb.band = nullptr;  // the force never goes through memory
-    q.coef = s->coef;
+    q.M = marker_slot(s, slot);
     q.c_num = (int)s->p.c_num;
-    q.c_space = (int)s->p.c_space;
-    q.T = (int)s->p.T;
-    q.p_step = s->p.p_step;
-    q.r_max = (int)(2 * kMarkersPerCilium / (double)s->p.c_space);  // main.cu:185
-    q.it = (int)s->it;
-    q.it_off = 0;
-    q.it_ptr = nullptr;
-    q.reach = s->reach_x;
     q.band_rows = s->band_rows;
     q.err = s->err_dev;
     return q;
 }
 
+// spreading fused into the LB kernel: whole channel on this GPU, vector path
 bool fused_path(const iblb_solver *s) {
     const bool coupled = s->connected && !(s->self_left && s->self_right);
     return s->p.c_num > 0 && s->fuse_ok && !coupled;
-}
-
-int launch_fused(iblb_solver *s, FusedParams &q, cudaStream_t st, unsigned long long &launches) {
-    dim3 g((unsigned)(s->L.YDIM / 64), (unsigned)((s->L.W + 7) / 8));
-    iblb_fused_step<<<g, 256, 0, st>>>(q);
-    launches += 1;
-    IBLB_CUDA(cudaGetLastError());
-    return IBLB_OK;
 }
 
 struct PhaseEvents {
@@ -57,7 +43,7 @@ struct PhaseEvents {
 int launch_lb(iblb_solver *s, const LbParams &q, cudaStream_t st, unsigned long long &launches) {
     if (q.col_count <= 0) return IBLB_OK;
     if (s->vec2) {
-        const long long n = (long long)q.col_count * (s->L.YDIM / 2);
+        const long long n = (long long)q.col_count * ((s->L.YDIM - q.row_begin) / 2);
         lb_fused_v2<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(q);
         launches += 1;
     } else {
@@ -83,8 +69,12 @@ int launch_lb(iblb_solver *s, const LbParams &q, cudaStream_t st, unsigned long 
     return IBLB_OK;
 }
 
-// One iteration: [slab wait] -> kinematics -> interpolate -> spread -> fused LB (boundary columns
-// first + signal, then interior, when coupled to other GPUs).
+// One iteration.
+//   whole channel on this GPU:  ib_markers -> lb_band_step            (2 launches; 3 on tall grids,
+//                               where lb_fused_v2 takes the rows above the force band)
+//   x-slab coupled to others:   [slab wait] -> ib_markers -> ib_spread -> lb_fused_v2 on the
+//                               boundary columns -> signal -> lb_fused_v2 on the interior
+// `pe`: time the phases separately (markers / spread / LB), which forces the unfused chain.
 int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEvents *pe,
                       unsigned long long &launches, int graph_it_off = 0) {
     const int src = s->cur;
@@ -100,39 +90,67 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         launches += 1;
     }
     if (pe) cudaEventRecord(pe->e[0], st);
-    if (!pe && fused_path(s)) {
-        FusedParams q = make_fused_params(s, src);
-        if (graph_mode) {
-            q.it_ptr = s->it_dev;
-            q.it = 0;
-            q.it_off = graph_it_off;
-        }
-        int rc = launch_fused(s, q, st, launches);
-        if (rc) return rc;
-        s->ib_stale = true;
-        s->cur ^= 1;
-        s->it += 1;
-        return IBLB_OK;
-    }
+    const bool fused = !pe && fused_path(s);
+    int slot = 0;
     if (s->p.c_num > 0) {
-        IbParams ib = make_ib_params(s, src);
-        if (graph_mode) ib.it_ptr = s->it_dev;
-        ib_kinematics<<<ib.c_num, 128, 0, st>>>(ib);
+        // marker kinematics, epsilon, spreading stencils: a batch of kKinBatch iterations at once
+        bool need_kin;
+        if (graph_mode) {
+            slot = graph_it_off;
+            need_kin = (graph_it_off == 0);
+        } else {
+            need_kin = s->kin_base < 0 || (long long)s->it < s->kin_base ||
+                       (long long)s->it >= s->kin_base + kKinBatch;
+            if (need_kin) s->kin_base = s->it;
+            slot = (int)((long long)s->it - s->kin_base);
+        }
+        if (need_kin) {
+            IbParams kp = make_ib_params(s, src, 0);
+            if (graph_mode) {
+                kp.it_ptr = s->it_dev;
+                kp.it = 0;
+            }
+            ib_kinematics_batch<<<dim3(kp.c_num, kKinBatch), 1024, 0, st>>>(kp);
+            launches += 1;
+            IBLB_CUDA(cudaGetLastError());
+        }
         if (pe) cudaEventRecord(pe->e[1], st);
-        ib_interpolate<<<(ib.Ns + 7) / 8, 256, 0, st>>>(ib);
-        if (pe) cudaEventRecord(pe->e[2], st);
-        dim3 g((s->L.W + kSpreadTileX - 1) / kSpreadTileX, s->band_rows / kSpreadTileY);
-        ib_spread<<<g, 256, 0, st>>>(ib);
-        launches += 3;
+        IbParams ib = make_ib_params(s, src, slot);
+        ib_interp<<<(ib.Ns + 23) / 24, 256, 0, st>>>(ib);
+        launches += 1;
         IBLB_CUDA(cudaGetLastError());
-        s->ib_stale = false;
+        if (pe) cudaEventRecord(pe->e[2], st);
+        if (!fused) {
+            dim3 g((s->L.W + kSpreadTileX - 1) / kSpreadTileX, s->band_rows / kSpreadTileY);
+            ib_spread<<<g, 256, 0, st>>>(ib);
+            launches += 1;
+            IBLB_CUDA(cudaGetLastError());
+            s->ib_stale = false;
+        }
     } else if (pe) {
         cudaEventRecord(pe->e[1], st);
         cudaEventRecord(pe->e[2], st);
     }
     if (pe) cudaEventRecord(pe->e[3], st);
     LbParams q = make_lb_params(s, src);
-    if (coupled) {
+    if (fused) {
+        BandParams bp = make_band_params(s, src, slot);
+        const int tiles_y = s->L.YDIM / 64, band_tiles = s->band_rows / 64;
+        // short channels: one launch for all row tiles; tall ones: band tiles here, the rest in
+        // lb_fused_v2 (leaner: no shared memory, 3 CTAs per SM)
+        const bool split = tiles_y > 8;
+        dim3 g((unsigned)(split ? band_tiles : tiles_y), (unsigned)((s->L.W + 7) / 8));
+        lb_band_step<<<g, 256, 0, st>>>(bp);
+        launches += 1;
+        IBLB_CUDA(cudaGetLastError());
+        if (split) {
+            q.band = nullptr;
+            q.row_begin = s->band_rows;
+            int rc = launch_lb(s, q, st, launches);
+            if (rc) return rc;
+        }
+        s->ib_stale = true;
+    } else if (coupled) {
         const int G = s->L.G, W = s->L.W;
         LbParams qb = q;  // boundary columns [0,G) and [W-G,W)
         qb.col_begin = 0;
@@ -165,18 +183,23 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
     return IBLB_OK;
 }
 
+// kGraphBatch iterations reading the iteration number from device memory, then it_advance
 int build_graph(iblb_solver *s) {
-    // two iterations (A->B, B->A); the iteration number is read from device memory
     cudaGraph_t graph = nullptr;
     const int cur0 = s->cur;
     const unsigned it0 = s->it;
+    const bool stale0 = s->ib_stale;
     unsigned long long dummy = 0;
     IBLB_CUDA(cudaStreamBeginCapture(s->stream, cudaStreamCaptureModeThreadLocal));
-    int rc = enqueue_iteration(s, s->stream, true, nullptr, dummy);
-    if (rc == IBLB_OK) rc = enqueue_iteration(s, s->stream, true, nullptr, dummy);
+    int rc = IBLB_OK;
+    for (unsigned i = 0; i < kGraphBatch && rc == IBLB_OK; i++)
+        rc = enqueue_iteration(s, s->stream, true, nullptr, dummy, (int)i);
+    if (rc == IBLB_OK && s->it_dev) it_advance<<<1, 32, 0, s->stream>>>(s->it_dev, (int)kGraphBatch);
     cudaError_t e = cudaStreamEndCapture(s->stream, &graph);
+    s->graph_launches = dummy + (s->it_dev ? 1 : 0);
     s->cur = cur0;
     s->it = it0;
+    s->ib_stale = stale0;
     if (rc != IBLB_OK) {
         if (graph) cudaGraphDestroy(graph);
         return rc;
@@ -188,39 +211,11 @@ int build_graph(iblb_solver *s) {
     return IBLB_OK;
 }
 
-// kFusedBatch fused iterations reading the iteration number from device memory, then it_advance
-int build_fused_graph(iblb_solver *s) {
-    cudaGraph_t graph = nullptr;
-    const int cur0 = s->cur;
-    const unsigned it0 = s->it;
-    unsigned long long dummy = 0;
-    IBLB_CUDA(cudaStreamBeginCapture(s->stream, cudaStreamCaptureModeThreadLocal));
-    int rc = IBLB_OK;
-    for (unsigned i = 0; i < kFusedBatch && rc == IBLB_OK; i++)
-        rc = enqueue_iteration(s, s->stream, true, nullptr, dummy, (int)i);
-    if (rc == IBLB_OK) it_advance<<<1, 32, 0, s->stream>>>(s->it_dev, (int)kFusedBatch);
-    cudaError_t e = cudaStreamEndCapture(s->stream, &graph);
-    s->cur = cur0;
-    s->it = it0;
-    if (rc != IBLB_OK) {
-        if (graph) cudaGraphDestroy(graph);
-        return rc;
-    }
-    if (e != cudaSuccess) return cuda_fail(e, "cudaStreamEndCapture");
-    e = cudaGraphInstantiate(&s->fused_graph, graph, 0);
-    cudaGraphDestroy(graph);
-    if (e != cudaSuccess) return cuda_fail(e, "cudaGraphInstantiate");
-    return IBLB_OK;
-}
-
-// the fused step keeps the IB state in shared memory only: rebuild the marker arrays and the force
-// band of the last completed iteration with the stand-alone kernels when somebody asks for them
+// lb_band_step consumes the spread force in registers: rebuild the force band of the last
+// completed iteration with the stand-alone spreading kernel when somebody asks for it
 int materialise_ib(iblb_solver *s) {
     if (!s->ib_stale || s->p.c_num == 0 || s->it == 0) return IBLB_OK;
-    IbParams ib = make_ib_params(s, s->cur ^ 1);
-    ib.it = (int)s->it - 1;
-    ib_kinematics<<<ib.c_num, 128, 0, s->stream>>>(ib);
-    ib_interpolate<<<(ib.Ns + 7) / 8, 256, 0, s->stream>>>(ib);
+    IbParams ib = make_ib_params(s, s->cur ^ 1, (int)((long long)s->it - 1 - s->kin_base));
     dim3 g((s->L.W + kSpreadTileX - 1) / kSpreadTileX, s->band_rows / kSpreadTileY);
     ib_spread<<<g, 256, 0, s->stream>>>(ib);
     IBLB_CUDA(cudaGetLastError());
@@ -234,9 +229,9 @@ int check_device_flag(iblb_solver *s) {
     IBLB_CUDA(cudaMemcpyAsync(&flag, s->err_dev, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
     IBLB_CUDA(cudaStreamSynchronize(s->stream));
     if (flag != 0) {
-        set_error(flag == 1 ? "fused step: a tile needs more cilia than kFusedMaxCilia "
+        set_error(flag == 1 ? "lb_band_step: more cilia overlap a tile than kBandMaxRel "
                               "(use IBLB_FLAG_NO_FUSE)"
-                            : "fused step: more markers touch a tile than kFusedMaxList "
+                            : "lb_band_step: more markers touch a tile than kBandMaxList "
                               "(use IBLB_FLAG_NO_FUSE)");
         return IBLB_EINVAL;
     }
@@ -257,49 +252,35 @@ int iblb_step(iblb_solver *s, unsigned n_steps) {
     unsigned long long launches = 0;
     IBLB_CUDA(cudaEventRecord(s->ev0, st));
     const bool coupled = s->connected && !(s->self_left && s->self_right);
-    // small grids are launch-bound: replay a captured two-iteration graph (needs cur == 0)
+    // small grids are launch-bound: replay captured batches of kGraphBatch iterations (captured
+    // with buffer A as the source: cur == 0)
     const long long nodes = (long long)s->L.W * s->L.YDIM;
     const bool use_graph = !(s->p.flags & IBLB_FLAG_NO_GRAPH) && !coupled && nodes <= (1 << 22) &&
-                           n_steps >= 4;
+                           n_steps >= kGraphBatch;
     unsigned left = n_steps;
-    if (use_graph && fused_path(s)) {
-        if (s->cur != 0 && left > 0) {
-            int rc = enqueue_iteration(s, st, false, nullptr, launches);
-            if (rc) return rc;
-            left--;
-        }
-        if (left >= kFusedBatch) {
-            if (!s->fused_graph) {
-                int rc = build_fused_graph(s);
-                if (rc) return rc;
-            }
-            IBLB_CUDA(cudaMemcpyAsync(s->it_dev, &s->it, sizeof(int), cudaMemcpyHostToDevice, st));
-            while (left >= kFusedBatch) {
-                IBLB_CUDA(cudaGraphLaunch(s->fused_graph, st));
-                s->it += kFusedBatch;
-                left -= kFusedBatch;
-                launches += kFusedBatch + 1;
-            }
-            s->ib_stale = true;
-        }
-    } else if (use_graph) {
+    if (use_graph) {
         if (s->cur != 0) {
             int rc = enqueue_iteration(s, st, false, nullptr, launches);
             if (rc) return rc;
             left--;
         }
-        if (!s->graph_exec) {
-            int rc = build_graph(s);
-            if (rc) return rc;
-        }
-        if (s->it_dev)
-            IBLB_CUDA(cudaMemcpyAsync(s->it_dev, &s->it, sizeof(int), cudaMemcpyHostToDevice, st));
-        const unsigned per_iter = s->p.c_num > 0 ? 4u : 1u;
-        while (left >= 2) {
-            IBLB_CUDA(cudaGraphLaunch(s->graph_exec, st));
-            s->it += 2;
-            left -= 2;
-            launches += 2 * per_iter;
+        if (left >= kGraphBatch) {
+            if (!s->graph_exec) {
+                int rc = build_graph(s);
+                if (rc) return rc;
+            }
+            if (s->it_dev)
+                IBLB_CUDA(cudaMemcpyAsync(s->it_dev, &s->it, sizeof(int), cudaMemcpyHostToDevice, st));
+            while (left >= kGraphBatch) {
+                IBLB_CUDA(cudaGraphLaunch(s->graph_exec, st));
+                s->it += kGraphBatch;
+                left -= kGraphBatch;
+                launches += s->graph_launches;
+            }
+            if (s->p.c_num > 0) {
+                s->ib_stale = fused_path(s);
+                s->kin_base = (long long)s->it - kGraphBatch;
+            }
         }
     }
     while (left > 0) {
@@ -430,11 +411,14 @@ int iblb_get_markers(iblb_solver *s, float *pos, float *vel, float *force, int *
         if (rc) return rc;
     }
     IBLB_CUDA(cudaStreamSynchronize(s->stream));
+    // marker state of the last completed iteration (slot of it-1; before the first step: zeros)
     const size_t nb = sizeof(float2) * s->Ns;
-    if (pos) IBLB_CUDA(cudaMemcpy(pos, s->M.s, nb, cudaMemcpyDeviceToHost));
-    if (vel) IBLB_CUDA(cudaMemcpy(vel, s->M.u_s, nb, cudaMemcpyDeviceToHost));
-    if (force) IBLB_CUDA(cudaMemcpy(force, s->M.F_s, nb, cudaMemcpyDeviceToHost));
-    if (eps) IBLB_CUDA(cudaMemcpy(eps, s->M.eps, sizeof(int) * s->Ns, cudaMemcpyDeviceToHost));
+    const int slot = (s->it > 0 && s->kin_base >= 0) ? (int)((long long)s->it - 1 - s->kin_base) : 0;
+    const MarkerArrays M = marker_slot(s, slot);
+    if (pos) IBLB_CUDA(cudaMemcpy(pos, M.s, nb, cudaMemcpyDeviceToHost));
+    if (vel) IBLB_CUDA(cudaMemcpy(vel, M.u_s, nb, cudaMemcpyDeviceToHost));
+    if (force) IBLB_CUDA(cudaMemcpy(force, M.F_s, nb, cudaMemcpyDeviceToHost));
+    if (eps) IBLB_CUDA(cudaMemcpy(eps, M.eps, sizeof(int) * s->Ns, cudaMemcpyDeviceToHost));
     return IBLB_OK;
 }
 

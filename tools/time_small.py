@@ -1,5 +1,5 @@
-"""Development timing (GPU box): per-step time of the cilia cases, fused single-launch step vs the
-four-kernel chain vs pure LB on the same grid.  IB share = (t_ib_run - t_pure_lb) / t_ib_run."""
+"""Development timing (GPU box): per-step time of the cilia cases, spreading fused into the LB kernel (2 launches) vs the
+unfused chain (3 launches) vs pure LB on the same grid.  IB share = (t_ib_run - t_pure_lb) / t_ib_run."""
 import os
 import sys
 
@@ -32,7 +32,15 @@ if __name__ == "__main__":
         fused_direct = t_step(Params.channel(X, Y, flags=FLAG_NO_GRAPH, **kw), n, 50)
         chain = t_step(Params.channel(X, Y, flags=FLAG_NO_FUSE, **kw), n, 50)
         lb = t_step(Params.channel(X, Y, gx=1e-7), n, 50)
-        print("%5dx%-5d %3d cilia: fused %.2f us (direct launches %.2f), 4-kernel chain %.2f, "
+        ph = Solver(Params.channel(X, Y, flags=FLAG_NO_GRAPH, **kw))
+        ph.step(20)
+        phases = ph.profile_phases(50)
+        ph.close()
+        print("      event-timed phases of the unfused chain (incl. ~2 us launch gap each): "
+              "markers %.2f spread %.2f lb %.2f us" % (
+                  1e6 * (phases["kinematics"] + phases["interpolate"]), 1e6 * phases["spread"],
+                  1e6 * phases["lb"]), flush=True)
+        print("%5dx%-5d %3d cilia: fused %.2f us (direct launches %.2f), unfused chain %.2f, "
               "pure LB %.2f us/step | %.0f MLUPS | IB share fused %.1f%% chain %.1f%%" % (
                   X, Y, cn, fused, fused_direct, chain, lb, X * Y / fused,
                   100 * (fused - lb) / fused, 100 * (chain - lb) / chain), flush=True)
