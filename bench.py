@@ -270,7 +270,9 @@ def run_ours(a):
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "%s: %s" % (a.workload, WORKLOADS[a.workload]["desc"]),
                        "grid": [int(p.XDIM), int(p.YDIM)], "columns_per_gpu": nodes_local // int(p.YDIM),
-                       "parallelism": "x-slabs x%d, NVLink peer-store halos" % n if n > 1 else "1 GPU",
+                       "parallelism": ("1 GPU" if n == 1 else "%d independent replicas, one per GPU" % n
+                                       if WORKLOADS[a.workload]["scaling"] == "replicas"
+                                       else "x-slabs x%d, NVLink peer-store halos" % n),
                        "l2_policy": "working set %.1f GB per GPU >> 126 MB L2" % (nodes_local * 144 / 1e9)
                        if nodes_local * 144 > 1e9 else "L2-resident (latency-bound case)"},
             "gpu_launches": launches_total,
@@ -370,8 +372,8 @@ def run_reference(a):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
