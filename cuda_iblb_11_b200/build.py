@@ -43,6 +43,8 @@ def build(force=False, verbose=False):
         cmd = ["nvcc", *ARCH, "-O3", "-lineinfo", "-std=c++17", "-shared", "-Xcompiler", "-fPIC",
                "-Xptxas", "-v", "-I", os.path.join(ROOT, "include"), "-I", CSRC,
                "-o", LIB, *srcs, "-lcudart"]
+        if os.environ.get("IBLB_TILE_TIMING"):  # development: per-CTA phase stamps
+            cmd.insert(1, "-DIBLB_TILE_TIMING")
         out = _run(cmd)
         if verbose:
             print(out)

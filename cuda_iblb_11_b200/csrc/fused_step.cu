@@ -1,16 +1,24 @@
-// LB step with the force spreading fused in: the second (and last) launch of an iteration.
+// One launch per iteration: immersed boundary and lattice Boltzmann in the same kernel.
 //
-//   launch 1  ib_markers      markers: kinematics, epsilon, F_s           (ib_kernels.cu)
-//   launch 2  lb_band_step    every node: [spread F_s ->] pull-stream, moments, TRT collide + Guo
+//   every kKinBatch iterations   ib_kinematics_batch   markers: kinematics, epsilon, stencils  (ib_kernels.cu)
+//                                ib_tile_lists         per tile and iteration: the ascending list of
+//                                                      markers whose 3x3 support can touch the tile
+//   every iteration              lb_ib_tile_step       F_s of the tile's markers -> spread -> pull-stream,
+//                                                      moments, TRT collide + Guo
 //
-// Replaces the reference's spread, streaming, macro, equilibrium, collision launches
-// (ImmersedBoundary.cu:138-267, LatticeBoltzmann.cu:30-411).  A CTA owns a tile of 8 columns x 64
-// rows (warp = column, lane = row pair).  Tiles of the forcing band (rows < 128) first build, by
-// ballot-ordered compaction (no atomics), the ascending list of markers whose 3x3 support can touch
-// the tile — cilia preselected by their bounding boxes — and every node sums its spreading terms in
-// ascending marker order, the order of ImmersedBoundary.cu:178-203.  The force never goes through
-// memory: it is consumed by the collision of the same thread.  The LB loads are issued before the
-// list is built, so their latency hides behind it.  Same device functions as lb_fused_v2 /
+// Replaces the reference's interpolate, spread, streaming, macro, equilibrium, collision launches
+// (ImmersedBoundary.cu:94-267, LatticeBoltzmann.cu:30-411).  A CTA owns a tile of 8 columns x 64
+// rows (warp = column, lane = row pair).  Everything about the markers that does not depend on the
+// fluid — positions, velocities, epsilon, delta factors AND which markers reach which tile — is
+// prescribed (main.cu:77-252 is a function of `it` alone) and is computed off the fluid's critical
+// path for a batch of iterations.  What is left per iteration is done by the tile that needs it: a
+// band tile computes F_s of the markers on its list straight from the post-collision populations
+// (nine support nodes x nine pulled populations each, ImmersedBoundary.cu:94-133; a marker that
+// reaches two tiles is evaluated by both: no inter-CTA dependency, no second launch, no atomics),
+// then every node sums its spreading terms in ascending marker order, the order of
+// ImmersedBoundary.cu:178-203.  Neither F_s nor the force goes through global memory: the force
+// is consumed by the collision of the same thread.  The LB loads are issued first, so their
+// latency hides behind the marker work.  Same device functions as lb_fused_v2 / ib_interp /
 // ib_spread: bit-identical results (tests/test_gpu_parity.py).
 #include "ib_device.cuh"
 #include "iblb_device.cuh"
@@ -18,14 +26,30 @@
 
 namespace iblb {
 
+// Development build (-DIBLB_TILE_TIMING): thread 0 of every CTA of lb_ib_tile_step stamps clock64()
+// at the phase boundaries into p.dbg[cta][16]; printed by iblb_destroy.  Not in product builds.
+#ifdef IBLB_TILE_TIMING
+#define TSTAMP(i)                                                                                  \
+    do {                                                                                           \
+        if (threadIdx.x == 0 && p.dbg)                                                             \
+            p.dbg[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 16 + (i)] = clock64();        \
+    } while (0)
+#else
+#define TSTAMP(i)
+#endif
+
 namespace {
 
-struct TileList {
-    // the markers that can touch the tile: (F_x, F_y, bx, by) and the 1-D delta factors of the
-    // columns bx..bx+3 / rows by..by+3 (tables written by ib_markers)
-    float4 fb[kBandMaxList], wx[kBandMaxList], wy[kBandMaxList];
-    short rel[kBandMaxRel];       // cilia whose bounding box overlaps the tile, ascending
-    int wcount[8];
+constexpr int kTabX = 12, kTabY = 68;  // the tile's 8x64 nodes plus two rings around them
+
+struct TileMarkers {
+    // the markers that can touch the tile: (F_x, F_y, bx, by), the 1-D delta factors of the columns
+    // bx..bx+3 / rows by..by+3 (tables written by ib_kinematics_batch), position and velocity
+    float4 fb[kTileCap], wx[kTileCap], wy[kTileCap], su[kTileCap];
+    // rho and u* of every node a support of these markers can contain: table[(x - (tx0-2))*kTabY +
+    // (y - (ty0-2))], x and y as the reference's interpolate counts them (unwrapped); rho = 0 marks
+    // a node that contributes nothing
+    double rho[kTabX * kTabY], ux[kTabX * kTabY], uy[kTabX * kTabY];
 };
 
 // ordered compaction helper: position of this thread's element among the taken ones of the CTA
@@ -47,86 +71,130 @@ __device__ __forceinline__ int cta_rank(bool take, int *wcount, int &total) {
     return r;
 }
 
-// Force on this thread's two nodes (global column xg, rows y0 and y0+1) from the markers.
-// All 256 threads of the CTA must call it.
-__device__ __forceinline__ void tile_spread(const BandParams &p, TileList &sh, int tile_x,
-                                            int tile_y, int xg, int y0, double &fx0, double &fy0,
-                                            double &fx1, double &fy1) {
-    const Lattice &L = p.lb.L;
-    const int t = threadIdx.x;
-    const float xlo = (float)(tile_x * 8 + L.x0) - 1.5f, xhi = (float)(tile_x * 8 + L.x0 + 7) + 1.5f;
-    const float ylo = (float)(tile_y * 64) - 1.5f, yhi = (float)(tile_y * 64 + 63) + 1.5f;
-    // ---- cilia whose bounding box of (wrapped) marker x overlaps the tile's reach ----
-    int nrel = 0;
-    for (int c0 = 0; c0 < p.c_num; c0 += 256) {
-        const int m = c0 + t;
-        bool rel = false;
-        if (m < p.c_num) {
-            const float2 bb = p.M.bbox[m];
-            rel = (bb.x <= xhi) && (bb.y >= xlo);
-        }
-        int total;
-        const int r = nrel + cta_rank(rel, sh.wcount, total);
-        if (rel && r < kBandMaxRel) sh.rel[r] = (short)m;
-        nrel += total;
+// moment-table cell of ring node idx in [0, kRingNodes)
+__device__ __forceinline__ int ring_cell(int idx) {
+    int lx, ly;
+    if (idx < 2 * kTabY) {  // two columns left of the tile
+        lx = idx / kTabY;
+        ly = idx - lx * kTabY;
+    } else if (idx < 4 * kTabY) {  // two columns right of it
+        const int r = idx - 2 * kTabY;
+        lx = r / kTabY;
+        ly = r - lx * kTabY;
+        lx += 10;
+    } else {  // two rows below, two above
+        const int r = idx - 4 * kTabY;
+        lx = 2 + (r & 7);
+        ly = (r >> 3) < 2 ? (r >> 3) : 64 + (r >> 3);
     }
-    if (nrel > kBandMaxRel) {
-        if (t == 0) atomicExch(p.err, 1);
-        return;
+    return lx * kTabY + ly;
+}
+
+// rho, u* of table cell c (a ring node, or an own node of a column past the channel), pulled from
+// global memory as the reference's interpolate would address it
+__device__ __forceinline__ void tile_pulled_cell(const Lattice &L, const double *__restrict__ src,
+                                                 TileMarkers &sh, int tx0, int ty0, int c) {
+    const int lx = c / kTabY, ly = c - lx * kTabY;
+    double rho, ux, uy;
+    if (!support_node_moments(L, src, tx0 - 2 + lx, ty0 - 2 + ly, rho, ux, uy)) rho = ux = uy = 0.;
+    sh.rho[c] = rho;
+    sh.ux[c] = ux;
+    sh.uy[c] = uy;
+}
+
+// rho and u* = sum c f / rho of pulled populations, same order as support_node_moments
+__device__ __forceinline__ void node_moments(const double (&f)[9], double &rho, double &ux,
+                                             double &uy) {
+    const double r = DA(DA(DA(DA(DA(DA(DA(DA(f[0], f[1]), f[2]), f[3]), f[4]), f[5]), f[6]), f[7]), f[8]);
+    rho = r;
+    ux = __ddiv_rn(DA(DS(DS(DA(DS(f[1], f[3]), f[5]), f[6]), f[7]), f[8]), r);
+    uy = __ddiv_rn(DS(DS(DA(DA(DS(f[2], f[4]), f[5]), f[6]), f[7]), f[8]), r);
+}
+
+// table cell of the centre of a marker's 3x3 support (ImmersedBoundary.cu:108-109: nearbyint of the
+// position); false when part of the support lies outside the table — only for a marker exactly 1.5
+// off the tile, whose every weight on the tile is 0 whatever its F_s
+__device__ __forceinline__ bool marker_centre_cell(float sx, float sy, int tx0, int ty0, int &c) {
+    const int x0 = (int)nearbyint((double)sx), y0 = (int)nearbyint((double)sy);
+    const int lx0 = x0 - (tx0 - 2), ly0 = y0 - (ty0 - 2);
+    c = lx0 * kTabY + ly0;
+    return lx0 >= 1 && lx0 <= kTabX - 2 && ly0 >= 1 && ly0 <= kTabY - 2;
+}
+
+// which of the 32 staged markers q0..q0+31 force the node pair (xg; y0, y0+1): stencil columns
+// bx..bx+3 contain xg and rows by..by+3 contain y0 or y0+1
+__device__ __forceinline__ unsigned hit_mask32(const int2 *base, int q0, int n, int xg, int y0) {
+    unsigned m = 0;
+    const int cnt = min(32, n - q0);
+    for (int e = 0; e < cnt; e++) {
+        const int2 b = base[q0 + e];
+        if ((unsigned)(xg - b.x) <= 3u && (unsigned)(y0 + 1 - b.y) <= 4u) m |= 1u << e;
     }
-    __syncthreads();
-    // ---- ascending (cilium, marker) list ----
-    int n = 0;
-    for (int c0 = 0; c0 < nrel * kMarkersPerCilium; c0 += 256) {
-        const int c = c0 + t;
-        bool take = false;
-        int k = 0;
-        if (c < nrel * kMarkersPerCilium) {
-            const int q = c / kMarkersPerCilium;
-            k = sh.rel[q] * kMarkersPerCilium + (c - q * kMarkersPerCilium);
-            const float2 sm = p.M.s[k];
-            take = (p.M.eps[k] != 0) && sm.x >= xlo && sm.x <= xhi && sm.y >= ylo && sm.y <= yhi;
+    return m;
+}
+
+// F_s of staged marker e (ImmersedBoundary.cu:94-133) from the moment table: nine terms in the
+// fixed order i = 0..8, the float re-rounded after each (Q6).  The delta factors are those of the
+// spreading stencil: support column x0+c is column bx + (x0+c-bx) of it, same expression, same bits.
+__device__ __forceinline__ void tile_marker_force(TileMarkers &sh, int tx0, int ty0, int e) {
+    const float4 su = sh.su[e], fb = sh.fb[e], wx = sh.wx[e], wy = sh.wy[e];
+    const int x0 = (int)nearbyint((double)su.x), y0 = (int)nearbyint((double)su.y);
+    const int bx = __float_as_int(fb.z), by = __float_as_int(fb.w);
+    const int ox = x0 - bx, oy = y0 - by;  // 1 or 2
+    const float dx[3] = {ox == 1 ? wx.x : wx.y, ox == 1 ? wx.y : wx.z, ox == 1 ? wx.z : wx.w};
+    const float dy[3] = {oy == 1 ? wy.x : wy.y, oy == 1 ? wy.y : wy.z, oy == 1 ? wy.z : wy.w};
+    float Fx = 0.f, Fy = 0.f;
+    int c0;
+    if (marker_centre_cell(su.x, su.y, tx0, ty0, c0)) {
+        // all products first (independent), then the two chains of float-rounded additions
+        double tx[9], ty[9];
+#pragma unroll
+        for (int i = 0; i < 9; i++) {
+            const int cx = i == 0 ? 0 : i == 1 ? 1 : i == 2 ? 0 : i == 3 ? -1 : i == 4 ? 0 : (i == 5 || i == 8) ? 1 : -1;
+            const int cy = i == 0 ? 0 : i == 1 ? 0 : i == 2 ? 1 : i == 3 ? 0 : i == 4 ? -1 : (i == 5 || i == 6) ? 1 : -1;
+            const int c = c0 + cx * kTabY + cy;
+            const double rho = sh.rho[c];
+            const float del = dx[cx + 1] * dy[cy + 1];  // float product (ImmersedBoundary.cu:78)
+            tx[i] = ty[i] = 0.;
+            if (rho != 0.) {
+                tx[i] = interp_product(del, rho, su.z, sh.ux[c]);
+                ty[i] = interp_product(del, rho, su.w, sh.uy[c]);
+            }
         }
-        int total;
-        const int r = n + cta_rank(take, sh.wcount, total);
-        if (take && r < kBandMaxList) {
-            const float2 F = p.M.F_s[k];
-            const int2 b = p.M.base[k];
-            sh.fb[r] = make_float4(F.x, F.y, __int_as_float(b.x), __int_as_float(b.y));
-            sh.wx[r] = p.M.wx[k];
-            sh.wy[r] = p.M.wy[k];
+#pragma unroll
+        for (int i = 0; i < 9; i++) {
+            Fx = (float)__dadd_rn((double)Fx, tx[i]);
+            Fy = (float)__dadd_rn((double)Fy, ty[i]);
         }
-        n += total;
     }
-    if (n > kBandMaxList) {
-        if (t == 0) atomicExch(p.err, 2);
-        return;
-    }
-    __syncthreads();
-    // ---- force = sum over markers (ascending) of (double)(F_s*delta [float product]) ----
-    // 32 entries at a time: the warp filters the markers whose stencil contains its column
-    // (ballot), every lane then keeps, as a bit mask, those that also reach one of its two rows
-    // and walks only its own few hits, lowest entry first: ascending order is preserved and the
-    // loop length is the ~8 markers that touch a node instead of the whole list.
-    const int lane = t & 31;
-    for (int q0 = 0; q0 < n; q0 += 32) {
-        bool hit = false;
-        int by_l = 0;
-        if (q0 + lane < n) {
-            const float4 fb = sh.fb[q0 + lane];
-            hit = (unsigned)(xg - __float_as_int(fb.z)) <= 3u;
-            by_l = __float_as_int(fb.w);
-        }
-        unsigned col = __ballot_sync(0xffffffffu, hit);
-        unsigned mine = 0;
-        while (col) {
-            const int e = __ffs(col) - 1;
-            col &= col - 1;
-            const int by_e = __shfl_sync(0xffffffffu, by_l, e);
-            if ((unsigned)(y0 + 1 - by_e) <= 4u) mine |= 1u << e;  // rows by..by+3 vs y0, y0+1
+    sh.fb[e].x = Fx;
+    sh.fb[e].y = Fy;
+}
+
+// Force on this thread's two nodes (global column xg, rows y0 and y0+1) from the n markers staged
+// in sh: sum over markers (ascending) of (double)(F_s*delta [float product]),
+// ImmersedBoundary.cu:196-197.  `hit` holds the precomputed masks of the first kHitWords*32 markers
+// (which of them reach one of the two nodes); the thread walks only its own few hits, lowest entry
+// first: ascending order is preserved and the loop length is the ~8 markers that touch a node.
+__device__ __forceinline__ void tile_spread(const TileMarkers &sh, int n, int xg, int y0,
+                                            const unsigned (&hit)[kHitWords], double &fx0,
+                                            double &fy0, double &fx1, double &fy1) {
+    for (int w = 0; w * 32 < n; w++) {
+        unsigned mine;
+        if (w < kHitWords) {
+            mine = w == 0 ? hit[0] : w == 1 ? hit[1] : w == 2 ? hit[2] : hit[3];
+        } else {  // long lists: found here
+            mine = 0;
+            const int cnt = min(32, n - w * 32);
+            for (int e = 0; e < cnt; e++) {
+                const float4 fb = sh.fb[w * 32 + e];
+                if ((unsigned)(xg - __float_as_int(fb.z)) <= 3u &&
+                    (unsigned)(y0 + 1 - __float_as_int(fb.w)) <= 4u)
+                    mine |= 1u << e;
+            }
         }
         while (mine) {
-            const int q = q0 + __ffs(mine) - 1;
+            const int q = w * 32 + __ffs(mine) - 1;
             mine &= mine - 1;
             const float4 fb = sh.fb[q], wx = sh.wx[q], wy = sh.wy[q];
             const int ix = xg - __float_as_int(fb.z);
@@ -148,37 +216,215 @@ __device__ __forceinline__ void tile_spread(const BandParams &p, TileList &sh, i
 
 }  // namespace
 
+// The fluid-independent plan of every band tile, for every iteration slot of a kinematics batch:
+// grid = (band row tiles, column tiles, slots).  Cilia are preselected by the bounding box of their
+// (wrapped) marker positions, then the markers with epsilon != 0 within 1.5 of the tile are kept by
+// ballot-ordered compaction (no atomics): the list is ascending in the marker index, which is the
+// summation order of the reference's spread (ImmersedBoundary.cu:178-203).  From the list follow
+// the per-thread hit masks of the spreading, and which nodes in and around the tile are support
+// nodes of the interpolation (ImmersedBoundary.cu:108-124) — the only ones whose moments the step
+// kernel has to form.
+__global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
+    __shared__ short rel[kBandMaxRel];  // cilia whose bounding box overlaps the tile, ascending
+    __shared__ int wcount[8];
+    __shared__ int slist[kTileCap];
+    __shared__ int2 sbase[kTileCap];
+    __shared__ unsigned char need[kTabX * kTabY];
+    const Lattice &L = p.lb.L;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int tile_y = blockIdx.x, tile_x = blockIdx.y, slot = blockIdx.z;
+    const long long mo = (long long)slot * p.Ns;
+    const float2 *__restrict__ bbox = p.M.bbox + (long long)slot * p.c_num;
+    const float2 *__restrict__ ms = p.M.s + mo;
+    const int *__restrict__ meps = p.M.eps + mo;
+    const int2 *__restrict__ mbase = p.M.base + mo;
+    TileProgram &pg = p.prog[((long long)slot * gridDim.x + tile_y) * p.tiles_x + tile_x];
+    const int tx0 = tile_x * 8 + L.x0, ty0 = tile_y * 64;
+    const float xlo = (float)tx0 - 1.5f, xhi = (float)(tx0 + 7) + 1.5f;
+    const float ylo = (float)ty0 - 1.5f, yhi = (float)(ty0 + 63) + 1.5f;
+    int nrel = 0;
+    for (int c0 = 0; c0 < p.c_num; c0 += 256) {
+        const int m = c0 + t;
+        bool take = false;
+        if (m < p.c_num) {
+            const float2 bb = bbox[m];
+            take = (bb.x <= xhi) && (bb.y >= xlo);
+        }
+        int total;
+        const int r = nrel + cta_rank(take, wcount, total);
+        if (take && r < kBandMaxRel) rel[r] = (short)m;
+        nrel += total;
+    }
+    if (nrel > kBandMaxRel) {
+        if (t == 0) {
+            atomicExch(p.err, 1);
+            pg.n = 0;
+            pg.nring = 0;
+        }
+        return;
+    }
+    __syncthreads();
+    int n = 0;
+    for (int c0 = 0; c0 < nrel * kMarkersPerCilium; c0 += 256) {
+        const int c = c0 + t;
+        bool take = false;
+        int k = 0;
+        if (c < nrel * kMarkersPerCilium) {
+            const int q = c / kMarkersPerCilium;
+            k = rel[q] * kMarkersPerCilium + (c - q * kMarkersPerCilium);
+            const float2 sm = ms[k];
+            take = (meps[k] != 0) && sm.x >= xlo && sm.x <= xhi && sm.y >= ylo && sm.y <= yhi;
+        }
+        int total;
+        const int r = n + cta_rank(take, wcount, total);
+        if (take && r < kTileCap) slist[r] = k;
+        n += total;
+    }
+    if (n > kTileCap) {
+        if (t == 0) atomicExch(p.err, 2);
+        n = 0;
+    }
+    for (int c = t; c < kTabX * kTabY; c += 256) need[c] = 0;
+    __syncthreads();
+    for (int e = t; e < n; e += 256) {
+        const int k = slist[e];
+        pg.list[e] = k;
+        sbase[e] = mbase[k];
+        const float2 sm = ms[k];
+        int c0;
+        if (marker_centre_cell(sm.x, sm.y, tx0, ty0, c0)) {
+#pragma unroll
+            for (int dx = -1; dx <= 1; dx++)
+#pragma unroll
+                for (int dy = -1; dy <= 1; dy++) need[c0 + dx * kTabY + dy] = 1;
+        }
+    }
+    __syncthreads();
+    // this thread's node pair in lb_ib_tile_step: column tx0 + warp, rows ty0 + 2*lane, +1
+#pragma unroll
+    for (int w = 0; w < kHitWords; w++)
+        pg.hit[w][t] = w * 32 < n ? hit_mask32(sbase, w * 32, n, tx0 + warp, ty0 + 2 * lane) : 0u;
+    {
+        const int c = (warp + 2) * kTabY + 2 * lane + 2;
+        pg.own[t] = (unsigned char)((need[c] ? 1 : 0) | (need[c + 1] ? 2 : 0));
+    }
+    int nring = 0;
+    for (int i0 = 0; i0 < kRingNodes; i0 += 256) {
+        const int idx = i0 + t;
+        const bool take = idx < kRingNodes && need[ring_cell(idx)] != 0;
+        int total;
+        const int r = nring + cta_rank(take, wcount, total);
+        if (take) pg.ring[r] = (short)idx;
+        nring += total;
+    }
+    if (t == 0) {
+        pg.n = n;
+        pg.nring = nring;
+    }
+}
+
 // grid = (row tiles, ceil(W/8)), block = 256.  Requires YDIM % 64 == 0 and a solver that owns the
 // whole channel (ghost columns = its own opposite edge).  Row tiles >= band_rows/64 are plain LB;
 // on tall grids only the band tiles are launched here and lb_fused_v2 takes the rows above.
-__global__ void __launch_bounds__(256, 3) lb_band_step(const BandParams p) {
-    __shared__ TileList sh;
+// p.M and p.prog point at the iteration's slot.
+__global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
+    __shared__ TileMarkers sh;  // 44 KB
     const LbParams &lp = p.lb;
     const Lattice &L = lp.L;
     const int tile_y = blockIdx.x, tile_x = blockIdx.y;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int x = tile_x * 8 + warp;
-    const int y0 = tile_y * 64 + 2 * lane;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int tx0 = tile_x * 8, ty0 = tile_y * 64;
+    const int x = tx0 + warp;
+    const int y0 = ty0 + 2 * lane;
     const bool active = x < L.W;  // warp-uniform
+    const bool band_tile = ty0 < p.band_rows;  // block-uniform
+    TSTAMP(0);
 
+    // the tile's plan first (the longest dependent chain), then the LB loads: both in flight
+    int n = 0, nring = 0;
+    const TileProgram *__restrict__ pg = nullptr;
+    if (band_tile) {
+        pg = p.prog + ((long long)tile_y * p.tiles_x + tile_x);
+        n = __ldg(&pg->n);
+        nring = __ldg(&pg->nring);
+    }
+    int k0 = 0, k1 = 0, r0 = 0, r1 = 0, own = 0;
+    unsigned hit[kHitWords] = {0u, 0u, 0u, 0u};
+    if (n > 0) {  // block-uniform
+        if (t < n) k0 = __ldg(pg->list + t);
+        if (t + 256 < n) k1 = __ldg(pg->list + t + 256);
+        if (t < nring) r0 = __ldg(pg->ring + t);
+        if (t + 256 < nring) r1 = __ldg(pg->ring + t + 256);
+        own = __ldg(pg->own + t);
+#pragma unroll
+        for (int w = 0; w < kHitWords; w++)
+            if (w * 32 < n) hit[w] = __ldg(&pg->hit[w][t]);
+    }
     Pulled q;
-    if (active) load_pulled(L, lp.src, x, y0, lane, q);  // in flight while the list is built
+    if (active) load_pulled(L, lp.src, x, y0, lane, q);
+    TSTAMP(1);
+#ifdef IBLB_TILE_TIMING
+    if (threadIdx.x == 0 && p.dbg) p.dbg[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 16 + 15] = n;
+#endif
+
+    if (n > 0) {
+        // marker data and the support nodes in the two rings around the tile: one more round trip
+#pragma unroll
+        for (int r = 0; r < 2; r++) {
+            const int e = t + 256 * r;
+            if (e < n) {
+                const int k = r ? k1 : k0;
+                const float2 sm = p.M.s[k], us = p.M.u_s[k];
+                const int2 b = p.M.base[k];
+                sh.su[e] = make_float4(sm.x, sm.y, us.x, us.y);
+                sh.fb[e] = make_float4(0.f, 0.f, __int_as_float(b.x), __int_as_float(b.y));
+                sh.wx[e] = p.M.wx[k];
+                sh.wy[e] = p.M.wy[k];
+            }
+        }
+        if (t < nring) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, ring_cell(r0));
+        if (t + 256 < nring) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, ring_cell(r1));
+        if (!active) {  // columns past the channel (W % 8 != 0): as the reference would address them
+            const int c = (warp + 2) * kTabY + 2 * lane + 2;
+            if (own & 1) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, c);
+            if (own & 2) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, c + 1);
+        }
+    }
+
+    TSTAMP(2);
+    double a[9], b[9];
+    if (active) shift_pulled(q, lane, a, b);
+    TSTAMP(3);
 
     double Fx0 = lp.gx, Fy0 = lp.gy, Fx1 = lp.gx, Fy1 = lp.gy;
     bool forced = (lp.gx != 0.0) | (lp.gy != 0.0);
-    if (tile_y * 64 < p.band_rows) {  // block-uniform
+    if (band_tile) forced = true;  // as the reference: spread's velocity update covers every node
+    if (n > 0) {
+        if (active) {  // this thread's support nodes: moments of the populations it pulled anyway
+            const int c = (warp + 2) * kTabY + 2 * lane + 2;
+            if (own & 1) node_moments(a, sh.rho[c], sh.ux[c], sh.uy[c]);
+            if (own & 2) node_moments(b, sh.rho[c + 1], sh.ux[c + 1], sh.uy[c + 1]);
+        }
+        TSTAMP(4);
+        __syncthreads();
+        TSTAMP(5);
+        if (t < n) tile_marker_force(sh, tx0 + L.x0, ty0, t);
+        if (t + 256 < n) tile_marker_force(sh, tx0 + L.x0, ty0, t + 256);
+        TSTAMP(6);
+        __syncthreads();
+        TSTAMP(7);
         double fx0 = 0., fy0 = 0., fx1 = 0., fy1 = 0.;
-        tile_spread(p, sh, tile_x, tile_y, x + L.x0, y0, fx0, fy0, fx1, fy1);
+        tile_spread(sh, n, x + L.x0, y0, hit, fx0, fy0, fx1, fy1);
         Fx0 += fx0; Fy0 += fy0; Fx1 += fx1; Fy1 += fy1;
-        forced = true;
+        TSTAMP(8);
     }
     if (!active) return;
 
-    double a[9], b[9];
-    shift_pulled(q, lane, a, b);
     const double ux0 = collide_node(a, Fx0, Fy0, forced, lp);
     const double ux1 = collide_node(b, Fx1, Fy1, forced, lp);
+    TSTAMP(9);
     store_pair(lp, x, y0, a, b);
+    TSTAMP(10);
 
     // flux through x = XDIM-5 (ImmersedBoundary.cu:259-264), same slots and order as lb_fused_v2
     if (x == lp.xq && lp.qacc != nullptr) {

@@ -88,26 +88,23 @@ __device__ __forceinline__ float delta_1d(float r) {
     return __dmul_rn(0.16667, __dsub_rn(__fma_rn(-3., rd, 5.), q));
 }
 
-// Term i (0..8) of the interpolation sum of marker (sm, us): 2*delta*rho*(u_s - u) at support node
-// i (ImmersedBoundary.cu:117-128), with rho and u of that node built from the nine populations it
-// pulls out of `src` (pull form of LatticeBoltzmann.cu:173-373, moments in the order of :396-405).
-// The reference indexes j = y*XDIM + x without wrapping (ImmersedBoundary.cu:119-122): x = -1 lands
-// on (XDIM-1, y-1), x = XDIM on (0, y+1); nodes outside the array contribute nothing here.
-__device__ __forceinline__ void interp_term(const Lattice &L, const double *__restrict__ src,
-                                            float2 sm, float2 us, int i, double &tx, double &ty) {
-    tx = 0.;
-    ty = 0.;
-    const double xs = sm.x, ys = sm.y;
-    const int x0 = (int)nearbyint(xs), y0 = (int)nearbyint(ys);
-    const int x = x0 + kCx[i], y = y0 + kCy[i];
+// rho and the uncorrected velocity u* (LatticeBoltzmann.cu:396-405, summation order i = 0..8) of
+// the node the reference's interpolate addresses as (x, y): it indexes j = y*XDIM + x WITHOUT
+// wrapping (ImmersedBoundary.cu:119-122), so x = -1 lands on (XDIM-1, y-1) and x = XDIM on
+// (0, y+1).  The node's nine populations are pulled out of the post-collision buffer `src` (pull
+// form of LatticeBoltzmann.cu:173-373 incl. the wall rules).  False when j lies outside the array
+// or the node's source columns are not held by this slab: such a node contributes nothing.
+__device__ __forceinline__ bool support_node_moments(const Lattice &L,
+                                                     const double *__restrict__ src, int x, int y,
+                                                     double &rho, double &ux, double &uy) {
     const long long j = (long long)y * L.XDIM + x;
-    if (j < 0 || j >= (long long)L.XDIM * L.YDIM) return;
+    if (j < 0 || j >= (long long)L.XDIM * L.YDIM) return false;
     const int ya = (int)(j / L.XDIM), xa = (int)(j - (long long)ya * L.XDIM);
     // global column -> a local column whose three source columns are present
     int xl = xa - L.x0;
     if (xl < -(L.G - 1)) xl += L.XDIM;
     else if (xl > L.W + L.G - 2) xl -= L.XDIM;
-    if (xl < -(L.G - 1) || xl > L.W + L.G - 2) return;
+    if (xl < -(L.G - 1) || xl > L.W + L.G - 2) return false;
     double f[9];
 #pragma unroll
     for (int q = 0; q < 9; q++) {
@@ -121,14 +118,35 @@ __device__ __forceinline__ void interp_term(const Lattice &L, const double *__re
         }
         f[q] = src[pi * L.plane + L.off(xsrc, ysrc)];
     }
-    const double rho = f[0] + f[1] + f[2] + f[3] + f[4] + f[5] + f[6] + f[7] + f[8];
-    const double ux = (f[1] - f[3] + f[5] - f[6] - f[7] + f[8]) / rho;
-    const double uy = (f[2] - f[4] + f[5] + f[6] - f[7] - f[8]) / rho;
+    rho = f[0] + f[1] + f[2] + f[3] + f[4] + f[5] + f[6] + f[7] + f[8];
+    ux = (f[1] - f[3] + f[5] - f[6] - f[7] + f[8]) / rho;
+    uy = (f[2] - f[4] + f[5] + f[6] - f[7] - f[8]) / rho;
+    return true;
+}
+
+// 2*delta*rho*(u_s - u), ImmersedBoundary.cu:126-127 evaluated left to right in double; `del` is
+// the float product of the two 1-D delta factors (ImmersedBoundary.cu:78).  Explicit intrinsics:
+// never contracted with the accumulation that follows, whatever kernel inlines it.
+__device__ __forceinline__ double interp_product(float del, double rho, float us, double u) {
+    return __dmul_rn(__dmul_rn(__dmul_rn(2., (double)del), rho), __dsub_rn((double)us, u));
+}
+
+// Term i (0..8) of the interpolation sum of marker (sm, us): 2*delta*rho*(u_s - u) at support node
+// i (ImmersedBoundary.cu:117-128).
+__device__ __forceinline__ void interp_term(const Lattice &L, const double *__restrict__ src,
+                                            float2 sm, float2 us, int i, double &tx, double &ty) {
+    tx = 0.;
+    ty = 0.;
+    const double xs = sm.x, ys = sm.y;
+    const int x0 = (int)nearbyint(xs), y0 = (int)nearbyint(ys);
+    const int x = x0 + kCx[i], y = y0 + kCy[i];
+    double rho, ux, uy;
+    if (!support_node_moments(L, src, x, y, rho, ux, uy)) return;
     const float dlx = delta_1d(fabsf(x - sm.x));
     const float dly = delta_1d(fabsf(y - sm.y));
-    const double del = dlx * dly;  // float product (ImmersedBoundary.cu:78)
-    tx = 2. * (1. * 1. * del) * rho * (us.x - ux);  // :126
-    ty = 2. * (1. * 1. * del) * rho * (us.y - uy);  // :127
+    const float del = dlx * dly;  // float product (ImmersedBoundary.cu:78)
+    tx = interp_product(del, rho, us.x, ux);
+    ty = interp_product(del, rho, us.y, uy);
 }
 
 }  // namespace

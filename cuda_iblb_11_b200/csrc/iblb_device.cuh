@@ -88,16 +88,34 @@ struct IbParams {
     int band_rows, band_ld;
 };
 
-// LB step with fused spreading (fused_step.cu)
-constexpr int kBandMaxRel = 128;   // cilia whose bounding box may overlap one 8-column tile
-constexpr int kBandMaxList = 512;  // markers whose support can touch one 8x64 tile
+// single-launch IB+LB iteration (fused_step.cu)
+constexpr int kBandMaxRel = 128;  // cilia whose bounding box may overlap one 8-column tile
+constexpr int kTileCap = 384;     // markers (epsilon != 0) whose support can touch one 8x64 tile
+constexpr int kHitWords = 4;      // precomputed 32-marker hit-mask words per thread
+constexpr int kRingNodes = 304;   // nodes of the two rings around an 8x64 tile
+
+// Everything about one band tile at one iteration that does not depend on the fluid (the cilia are
+// prescribed), written by ib_tile_lists for a batch of iterations, read by lb_ib_tile_step.
+struct TileProgram {
+    int n;                        // markers (epsilon != 0) whose 3x3 support can touch the tile
+    int nring;                    // ring nodes that are support nodes of these markers
+    int pad[2];
+    int list[kTileCap];           // their indices, ascending (the reference's summation order)
+    unsigned hit[kHitWords][256]; // per thread (node pair): which of list[32w..32w+31] force its nodes
+    short ring[kRingNodes];       // the needed ring nodes
+    unsigned char own[256];       // per thread: bit 0/1 = node y0 / y0+1 is a support node
+};
+static_assert(sizeof(TileProgram) % 16 == 0, "TileProgram alignment");
 
 struct BandParams {
     LbParams lb;
-    MarkerArrays M;
-    int c_num;
+    MarkerArrays M;          // ib_tile_lists: slot 0; lb_ib_tile_step: the iteration's slot
+    int c_num, Ns;
     int band_rows;           // rows that can receive IB force (multiple of 64)
-    int *err;                // set non-zero when a tile exceeds kBandMaxRel / kBandMaxList
+    int tiles_x;             // column tiles = ceil(W/8)
+    TileProgram *prog;       // [slot][band row tile][column tile]
+    int *err;                // set non-zero when a tile exceeds kBandMaxRel / kTileCap
+    long long *dbg;          // development timing stamps (IBLB_TILE_TIMING builds) or nullptr
 };
 
 }  // namespace iblb

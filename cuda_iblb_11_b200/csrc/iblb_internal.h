@@ -30,7 +30,8 @@ __global__ void ib_coef(const int *k_of_j, float *coef);
 __global__ void ib_kinematics_batch(const IbParams p);
 __global__ void ib_interp(const IbParams p);
 __global__ void ib_spread(const IbParams p);
-__global__ void lb_band_step(const BandParams p);
+__global__ void ib_tile_lists(const BandParams p);
+__global__ void lb_ib_tile_step(const BandParams p);
 __global__ void it_advance(int *it_ptr, int by);
 __global__ void slab_wait(const volatile int *flag_l, const volatile int *flag_r, int need);
 __global__ void slab_signal(int *left_flag, int *right_flag, int value);
@@ -55,9 +56,13 @@ struct iblb_solver {
     int band_rows, band_ld;
     int *it_dev;               // device copy of `it` read by the graph-captured kinematics
     long long kin_base;        // marker slots hold iterations [kin_base, kin_base + kKinBatch); -1: none
-    // two-launch iteration: ib_markers + lb_band_step (spreading fused into the LB kernel)
+    // single-launch iteration: lb_ib_tile_step (interpolation and spreading inside the LB kernel)
     bool fuse_ok;              // geometry allows it (whole channel, YDIM % 64 == 0)
-    bool ib_stale;             // force band not materialised for the last step
+    bool ib_stale;             // F_s / force band not materialised for the last step
+    iblb::TileProgram *prog;   // per slot and band tile: fluid-independent plan (ib_tile_lists)
+    int tiles_x, band_tiles;   // column tiles, band row tiles
+    long long *dbg_dev;        // development timing stamps (IBLB_TILE_TIMING builds)
+    long long lists_base;      // tile lists hold iterations [lists_base, lists_base + kKinBatch); -1: none
     float reach_x, reach_y;    // bounds on the marker excursion from the cilium base
     int *err_dev;
     // flux

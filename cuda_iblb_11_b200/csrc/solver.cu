@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <vector>
 
 #include "iblb_internal.h"
 
@@ -113,6 +114,7 @@ static int init_state(iblb_solver *s, const double *rho_dev, const double *u_dev
     s->cur = 0;
     s->ib_stale = false;
     s->kin_base = -1;
+    s->lists_base = -1;
     s->flag_base += (int)s->it;  // all slabs reset together: later flag values stay above old ones
     s->it = 0;
     IBLB_CUDA(cudaStreamSynchronize(s->stream));
@@ -257,6 +259,22 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
             return IBLB_EINVAL;
         }
         s->fuse_ok = !slab && s->vec2 && !(p.flags & IBLB_FLAG_NO_FUSE);
+        if (s->fuse_ok) {
+            s->tiles_x = (L.W + 7) / 8;
+            s->band_tiles = s->band_rows / 64;
+            const size_t nt = (size_t)kKinBatch * s->band_tiles * s->tiles_x;
+            cudaError_t e = cudaMalloc((void **)&s->prog, sizeof(TileProgram) * nt);
+            if (e == cudaSuccess) e = cudaMemset(s->prog, 0, sizeof(TileProgram) * nt);
+#ifdef IBLB_TILE_TIMING
+            const size_t nd = (size_t)(L.YDIM / 64) * s->tiles_x * 16;
+            if (e == cudaSuccess) e = cudaMalloc((void **)&s->dbg_dev, sizeof(long long) * nd);
+            if (e == cudaSuccess) e = cudaMemset(s->dbg_dev, 0, sizeof(long long) * nd);
+#endif
+            if (e != cudaSuccess) {
+                iblb_destroy(s);
+                return cuda_fail(e, "cudaMalloc(tile lists)");
+            }
+        }
     }
     // a lone solver is periodic with itself
     for (int b = 0; b < 2; b++) {
@@ -282,6 +300,26 @@ int iblb_destroy(iblb_solver *s) {
     if (!s) return IBLB_OK;
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
+#ifdef IBLB_TILE_TIMING
+    if (s->dbg_dev) {  // phase stamps of the last lb_ib_tile_step launch, per CTA
+        const int ty = s->L.YDIM / 64 > 8 ? s->band_tiles : s->L.YDIM / 64;
+        const size_t nc = (size_t)ty * s->tiles_x;
+        std::vector<long long> h(nc * 16);
+        cudaMemcpy(h.data(), s->dbg_dev, sizeof(long long) * nc * 16, cudaMemcpyDeviceToHost);
+        size_t worst = 0;
+        double avg[11] = {0};
+        for (size_t c = 0; c < nc; c++) {
+            if (h[c * 16 + 10] - h[c * 16] > h[worst * 16 + 10] - h[worst * 16]) worst = c;
+            for (int i = 1; i <= 10; i++) avg[i] += (double)(h[c * 16 + i] - h[c * 16]) / nc;
+        }
+        fprintf(stderr, "tile timing (%zu CTAs), cycles since CTA start: avg", nc);
+        for (int i = 1; i <= 10; i++) fprintf(stderr, " %.0f", avg[i]);
+        fprintf(stderr, "\n  worst CTA %zu (n=%lld):", worst, h[worst * 16 + 15]);
+        for (int i = 1; i <= 10; i++) fprintf(stderr, " %lld", h[worst * 16 + i] - h[worst * 16]);
+        fprintf(stderr, "\n");
+        cudaFree(s->dbg_dev);
+    }
+#endif
     if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
     cudaFree(s->err_dev);
     for (int f = 0; f < 2; f++) {
@@ -294,6 +332,7 @@ int iblb_destroy(iblb_solver *s) {
     cudaFree(s->M.F_s); cudaFree(s->M.eps); cudaFree(s->M.bbox); cudaFree(s->coef);
     cudaFree(s->M.wx); cudaFree(s->M.wy); cudaFree(s->M.base);
     cudaFree(s->k_of_j_dev); cudaFree(s->it_dev);
+    cudaFree(s->prog);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->ev_boundary) cudaEventDestroy(s->ev_boundary);

@@ -24,8 +24,12 @@ BandParams make_band_params(const iblb_solver *s, int src_idx, int slot) {
     q.lb.band = nullptr;  // the force never goes through memory
     q.M = marker_slot(s, slot);
     q.c_num = (int)s->p.c_num;
+    q.Ns = s->Ns;
     q.band_rows = s->band_rows;
+    q.tiles_x = s->tiles_x;
+    q.prog = s->prog + (size_t)slot * s->band_tiles * s->tiles_x;
     q.err = s->err_dev;
+    q.dbg = s->dbg_dev;
     return q;
 }
 
@@ -70,8 +74,9 @@ int launch_lb(iblb_solver *s, const LbParams &q, cudaStream_t st, unsigned long 
 }
 
 // One iteration.
-//   whole channel on this GPU:  ib_markers -> lb_band_step            (2 launches; 3 on tall grids,
-//                               where lb_fused_v2 takes the rows above the force band)
+//   whole channel on this GPU:  lb_ib_tile_step: ONE launch (2 on tall grids, where lb_fused_v2
+//                               takes the rows above the force band), plus, once per kKinBatch
+//                               iterations, ib_kinematics_batch + ib_tile_lists
 //   x-slab coupled to others:   [slab wait] -> ib_markers -> ib_spread -> lb_fused_v2 on the
 //                               boundary columns -> signal -> lb_fused_v2 on the interior
 // `pe`: time the phases separately (markers / spread / LB), which forces the unfused chain.
@@ -114,11 +119,24 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
             launches += 1;
             IBLB_CUDA(cudaGetLastError());
         }
+        if (fused) {
+            // which markers reach which tile, for the same batch of iterations
+            const bool need_lists = graph_mode ? need_kin : (s->lists_base != s->kin_base);
+            if (need_lists) {
+                BandParams lp = make_band_params(s, src, 0);
+                ib_tile_lists<<<dim3(s->band_tiles, s->tiles_x, kKinBatch), 256, 0, st>>>(lp);
+                launches += 1;
+                IBLB_CUDA(cudaGetLastError());
+                if (!graph_mode) s->lists_base = s->kin_base;
+            }
+        }
         if (pe) cudaEventRecord(pe->e[1], st);
         IbParams ib = make_ib_params(s, src, slot);
-        ib_interp<<<(ib.Ns + 23) / 24, 256, 0, st>>>(ib);
-        launches += 1;
-        IBLB_CUDA(cudaGetLastError());
+        if (!fused) {
+            ib_interp<<<(ib.Ns + 23) / 24, 256, 0, st>>>(ib);
+            launches += 1;
+            IBLB_CUDA(cudaGetLastError());
+        }
         if (pe) cudaEventRecord(pe->e[2], st);
         if (!fused) {
             dim3 g((s->L.W + kSpreadTileX - 1) / kSpreadTileX, s->band_rows / kSpreadTileY);
@@ -139,8 +157,8 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         // short channels: one launch for all row tiles; tall ones: band tiles here, the rest in
         // lb_fused_v2 (leaner: no shared memory, 3 CTAs per SM)
         const bool split = tiles_y > 8;
-        dim3 g((unsigned)(split ? band_tiles : tiles_y), (unsigned)((s->L.W + 7) / 8));
-        lb_band_step<<<g, 256, 0, st>>>(bp);
+        dim3 g((unsigned)(split ? band_tiles : tiles_y), (unsigned)s->tiles_x);
+        lb_ib_tile_step<<<g, 256, 0, st>>>(bp);
         launches += 1;
         IBLB_CUDA(cudaGetLastError());
         if (split) {
@@ -211,11 +229,14 @@ int build_graph(iblb_solver *s) {
     return IBLB_OK;
 }
 
-// lb_band_step consumes the spread force in registers: rebuild the force band of the last
-// completed iteration with the stand-alone spreading kernel when somebody asks for it
+// lb_ib_tile_step keeps F_s in shared memory and consumes the spread force in registers: rebuild
+// F_s and the force band of the last completed iteration with the stand-alone kernels when
+// somebody asks for them
 int materialise_ib(iblb_solver *s) {
     if (!s->ib_stale || s->p.c_num == 0 || s->it == 0) return IBLB_OK;
     IbParams ib = make_ib_params(s, s->cur ^ 1, (int)((long long)s->it - 1 - s->kin_base));
+    ib_interp<<<(ib.Ns + 23) / 24, 256, 0, s->stream>>>(ib);
+    IBLB_CUDA(cudaGetLastError());
     dim3 g((s->L.W + kSpreadTileX - 1) / kSpreadTileX, s->band_rows / kSpreadTileY);
     ib_spread<<<g, 256, 0, s->stream>>>(ib);
     IBLB_CUDA(cudaGetLastError());
@@ -229,9 +250,9 @@ int check_device_flag(iblb_solver *s) {
     IBLB_CUDA(cudaMemcpyAsync(&flag, s->err_dev, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
     IBLB_CUDA(cudaStreamSynchronize(s->stream));
     if (flag != 0) {
-        set_error(flag == 1 ? "lb_band_step: more cilia overlap a tile than kBandMaxRel "
+        set_error(flag == 1 ? "ib_tile_lists: more cilia overlap a tile than kBandMaxRel "
                               "(use IBLB_FLAG_NO_FUSE)"
-                            : "lb_band_step: more markers touch a tile than kBandMaxList "
+                            : "ib_tile_lists: more markers touch a tile than kTileCap "
                               "(use IBLB_FLAG_NO_FUSE)");
         return IBLB_EINVAL;
     }
@@ -280,6 +301,7 @@ int iblb_step(iblb_solver *s, unsigned n_steps) {
             if (s->p.c_num > 0) {
                 s->ib_stale = fused_path(s);
                 s->kin_base = (long long)s->it - kGraphBatch;
+                s->lists_base = s->ib_stale ? s->kin_base : -1;
             }
         }
     }

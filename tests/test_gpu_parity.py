@@ -254,8 +254,8 @@ def test_graph_replay_equals_direct_launches():
     (16, 128, 16, 192), (5, 40, 2, 192), (2, 192, 1, 128),
 ])
 def test_fused_single_launch_step_equals_separate_kernels(c_num, c_space, c_fraction, Y):
-    """Spreading fused into the LB kernel (default: ib_interp + lb_band_step, two launches per
-    iteration) and the unfused chain (IBLB_FLAG_NO_FUSE: ib_interp, ib_spread, lb_fused_v2) run
+    """Interpolation and spreading fused into the LB kernel (default: lb_ib_tile_step, ONE launch
+    per iteration) and the unfused chain (IBLB_FLAG_NO_FUSE: ib_interp, ib_spread, lb_fused_v2) run
     the same device functions in the same order: bit-identical state, with and without CUDA-graph
     batches."""
     X = c_num * c_space
@@ -266,9 +266,9 @@ def test_fused_single_launch_step_equals_separate_kernels(c_num, c_space, c_frac
     for n in (1, 2, 17, 9):
         for s in (a, b, c):
             s.step(n)
-        # two launches an iteration (ib_interp, lb_band_step) + the kinematics batch / counter
+        # one launch an iteration (lb_ib_tile_step) + kinematics batch, tile lists and counter
         # update once per 8 iterations; three an iteration unfused
-        assert a.last_step_launches <= 2 * n + 2 * (n // 8) + 3
+        assert a.last_step_launches <= n + 3 * (n // 8) + 6
         assert 3 * n <= b.last_step_launches <= 3 * n + n // 8 + 1
         ref = (b.fields(), b.markers(), b.force(), b.populations())
         for s in (a, c):

@@ -1,3 +1,4 @@
+# per-kernel durations of the warm C3 step (ncu, no cache/clock control)
 set -x
 mkdir -p gpurun_out
 ncu --metrics gpu__time_duration.sum --cache-control none --clock-control none -s 200 -c 300 --csv --log-file gpurun_out/launches_c3_warm.csv \

@@ -1,0 +1,8 @@
+# GPU-box batch K (TileProgram): single-launch IB+LB iteration — tests, small-grid timing, C3/C1 bench.
+set -x
+mkdir -p gpurun_out
+python -m pytest tests -m gpu -q --timeout 900 -x > gpurun_out/pytest_gpu_k.log 2>&1; echo "pytest rc=$?"
+python tools/time_small.py 4 > gpurun_out/time_small_k.log 2>&1
+python bench.py --workload c3 --steps 4000 --warmup 100 --no-cpu-baseline > gpurun_out/bench_c3_k.json 2> gpurun_out/bench_c3_k.err
+python bench.py --workload c1 --steps 4000 --warmup 100 --no-cpu-baseline > gpurun_out/bench_c1_k.json 2> gpurun_out/bench_c1_k.err
+tail -n 15 gpurun_out/pytest_gpu_k.log; cat gpurun_out/time_small_k.log; cut -c1-200 gpurun_out/bench_c3_k.json gpurun_out/bench_c1_k.json
