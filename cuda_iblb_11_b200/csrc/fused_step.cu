@@ -40,6 +40,12 @@ namespace iblb {
 
 namespace {
 
+// programmatic dependent launch (PTX griddepcontrol); no-ops in a launch without the attribute
+__device__ __forceinline__ void pdl_launch_dependents() {
+    asm volatile("griddepcontrol.launch_dependents;");
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 constexpr int kTabX = 12, kTabY = 68;  // the tile's 8x64 nodes plus two rings around them
 
 struct TileMarkers {
@@ -193,23 +199,26 @@ __device__ __forceinline__ void tile_spread(const TileMarkers &sh, int n, int xg
                     mine |= 1u << e;
             }
         }
+        // branch-free body: a row the marker does not reach gets delta 0, and adding the resulting
+        // +-0 leaves the sum as it is (it starts at +0 and can never become -0) — the reference
+        // itself adds every marker to every node, zeros included (ImmersedBoundary.cu:194-197)
+        const float *__restrict__ wxs = reinterpret_cast<const float *>(sh.wx);
+        const float *__restrict__ wys = reinterpret_cast<const float *>(sh.wy);
         while (mine) {
             const int q = w * 32 + __ffs(mine) - 1;
             mine &= mine - 1;
-            const float4 fb = sh.fb[q], wx = sh.wx[q], wy = sh.wy[q];
-            const int ix = xg - __float_as_int(fb.z);
-            const int iy = y0 - __float_as_int(fb.w);  // row y0; row y0+1 is iy+1
-            const float ddx = ix == 0 ? wx.x : ix == 1 ? wx.y : ix == 2 ? wx.z : wx.w;
-            if (iy >= 0 && iy <= 3) {
-                const float del = ddx * (iy == 0 ? wy.x : iy == 1 ? wy.y : iy == 2 ? wy.z : wy.w);
-                fx0 += (double)(fb.x * del);
-                fy0 += (double)(fb.y * del);
-            }
-            if (iy >= -1 && iy <= 2) {
-                const float del = ddx * (iy == -1 ? wy.x : iy == 0 ? wy.y : iy == 1 ? wy.z : wy.w);
-                fx1 += (double)(fb.x * del);
-                fy1 += (double)(fb.y * del);
-            }
+            const float4 fb = sh.fb[q];
+            const int ix = xg - __float_as_int(fb.z);  // 0..3 for a hit
+            const int iy = y0 - __float_as_int(fb.w);  // row y0; row y0+1 is iy+1; -1..3 for a hit
+            const float ddx = wxs[4 * q + ix];
+            const float wa = wys[4 * q + max(iy, 0)];
+            const float wb = wys[4 * q + min(iy + 1, 3)];
+            const float del0 = iy >= 0 ? ddx * wa : 0.f;
+            const float del1 = iy <= 2 ? ddx * wb : 0.f;
+            fx0 += (double)(fb.x * del0);
+            fy0 += (double)(fb.y * del0);
+            fx1 += (double)(fb.x * del1);
+            fy1 += (double)(fb.y * del1);
         }
     }
 }
@@ -340,7 +349,12 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
     const bool band_tile = ty0 < p.band_rows;  // block-uniform
     TSTAMP(0);
 
-    // the tile's plan first (the longest dependent chain), then the LB loads: both in flight
+    // Programmatic dependent launch: the next iteration's CTAs may start as soon as every CTA of
+    // this one is running.  Everything up to pdl_wait() reads only the prescribed marker data (the
+    // tile's plan and its markers, written by kernels that completed before the first kernel of this
+    // PDL chain started), so it overlaps the tail of the previous iteration; pdl_wait() returns once
+    // the previous iteration has completed and its populations are visible.
+    pdl_launch_dependents();
     int n = 0, nring = 0;
     const TileProgram *__restrict__ pg = nullptr;
     if (band_tile) {
@@ -348,9 +362,10 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
         n = __ldg(&pg->n);
         nring = __ldg(&pg->nring);
     }
-    int k0 = 0, k1 = 0, r0 = 0, r1 = 0, own = 0;
+    int r0 = 0, r1 = 0, own = 0;
     unsigned hit[kHitWords] = {0u, 0u, 0u, 0u};
     if (n > 0) {  // block-uniform
+        int k0 = 0, k1 = 0;
         if (t < n) k0 = __ldg(pg->list + t);
         if (t + 256 < n) k1 = __ldg(pg->list + t + 256);
         if (t < nring) r0 = __ldg(pg->ring + t);
@@ -359,16 +374,6 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
 #pragma unroll
         for (int w = 0; w < kHitWords; w++)
             if (w * 32 < n) hit[w] = __ldg(&pg->hit[w][t]);
-    }
-    Pulled q;
-    if (active) load_pulled(L, lp.src, x, y0, lane, q);
-    TSTAMP(1);
-#ifdef IBLB_TILE_TIMING
-    if (threadIdx.x == 0 && p.dbg) p.dbg[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 16 + 15] = n;
-#endif
-
-    if (n > 0) {
-        // marker data and the support nodes in the two rings around the tile: one more round trip
 #pragma unroll
         for (int r = 0; r < 2; r++) {
             const int e = t + 256 * r;
@@ -382,6 +387,17 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
                 sh.wy[e] = p.M.wy[k];
             }
         }
+    }
+    pdl_wait();
+    TSTAMP(1);
+    Pulled q;
+    if (active) load_pulled(L, lp.src, x, y0, lane, q);
+#ifdef IBLB_TILE_TIMING
+    if (threadIdx.x == 0 && p.dbg) p.dbg[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 16 + 15] = n;
+#endif
+
+    if (n > 0) {
+        // the support nodes in the two rings around the tile
         if (t < nring) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, ring_cell(r0));
         if (t + 256 < nring) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, ring_cell(r1));
         if (!active) {  // columns past the channel (W % 8 != 0): as the reference would address them

@@ -99,7 +99,11 @@ __device__ __forceinline__ bool support_node_moments(const Lattice &L,
                                                      double &rho, double &ux, double &uy) {
     const long long j = (long long)y * L.XDIM + x;
     if (j < 0 || j >= (long long)L.XDIM * L.YDIM) return false;
-    const int ya = (int)(j / L.XDIM), xa = (int)(j - (long long)ya * L.XDIM);
+    int ya = y, xa = x;
+    if ((unsigned)x >= (unsigned)L.XDIM) {  // off the row: the division only here
+        ya = (int)(j / L.XDIM);
+        xa = (int)(j - (long long)ya * L.XDIM);
+    }
     // global column -> a local column whose three source columns are present
     int xl = xa - L.x0;
     if (xl < -(L.G - 1)) xl += L.XDIM;

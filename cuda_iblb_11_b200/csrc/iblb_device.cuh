@@ -21,7 +21,7 @@ constexpr double kCs = 0.57735;  // device sound speed, LatticeBoltzmann.cu:11 (
 constexpr int kMarkersPerCilium = 96;   // main.cu:83
 constexpr int kFinePoints = 9600;       // main.cu:81
 constexpr int kSpreadTileX = 8, kSpreadTileY = 32;
-constexpr int kKinBatch = 8;       // iterations of marker kinematics computed per launch
+constexpr int kKinBatch = 32;      // iterations of marker kinematics computed per launch
 constexpr int kMaxLeftCilia = 16;  // r_max = 2*96/c_space (main.cu:185) must not exceed this
 
 struct Lattice {

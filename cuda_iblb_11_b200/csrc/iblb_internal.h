@@ -59,6 +59,7 @@ struct iblb_solver {
     // single-launch iteration: lb_ib_tile_step (interpolation and spreading inside the LB kernel)
     bool fuse_ok;              // geometry allows it (whole channel, YDIM % 64 == 0)
     bool ib_stale;             // F_s / force band not materialised for the last step
+    bool pdl_chain;            // the last kernel enqueued was lb_ib_tile_step over the whole grid
     iblb::TileProgram *prog;   // per slot and band tile: fluid-independent plan (ib_tile_lists)
     int tiles_x, band_tiles;   // column tiles, band row tiles
     long long *dbg_dev;        // development timing stamps (IBLB_TILE_TIMING builds)

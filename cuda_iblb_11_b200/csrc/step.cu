@@ -96,6 +96,9 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
     }
     if (pe) cudaEventRecord(pe->e[0], st);
     const bool fused = !pe && fused_path(s);
+    const bool chain = s->pdl_chain;  // the previous kernel in the stream is lb_ib_tile_step
+    s->pdl_chain = false;
+    bool fresh_plan = false;          // this iteration launched what the fused prologue reads
     int slot = 0;
     if (s->p.c_num > 0) {
         // marker kinematics, epsilon, spreading stencils: a batch of kKinBatch iterations at once
@@ -116,6 +119,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
                 kp.it = 0;
             }
             ib_kinematics_batch<<<dim3(kp.c_num, kKinBatch), 1024, 0, st>>>(kp);
+            fresh_plan = true;
             launches += 1;
             IBLB_CUDA(cudaGetLastError());
         }
@@ -125,6 +129,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
             if (need_lists) {
                 BandParams lp = make_band_params(s, src, 0);
                 ib_tile_lists<<<dim3(s->band_tiles, s->tiles_x, kKinBatch), 256, 0, st>>>(lp);
+                fresh_plan = true;
                 launches += 1;
                 IBLB_CUDA(cudaGetLastError());
                 if (!graph_mode) s->lists_base = s->kin_base;
@@ -158,9 +163,24 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         // lb_fused_v2 (leaner: no shared memory, 3 CTAs per SM)
         const bool split = tiles_y > 8;
         dim3 g((unsigned)(split ? band_tiles : tiles_y), (unsigned)s->tiles_x);
-        lb_ib_tile_step<<<g, 256, 0, st>>>(bp);
+        // Programmatic dependent launch behind the previous iteration's lb_ib_tile_step: the
+        // kernel's fluid-independent prologue overlaps that kernel's tail.  Not right behind the
+        // kernels that write what the prologue reads (kinematics, tile lists), and not on tall
+        // grids, where lb_fused_v2 of the previous iteration is the predecessor.
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof cfg);
+        cfg.gridDim = g;
+        cfg.blockDim = dim3(256);
+        cfg.stream = st;
+        cudaLaunchAttribute attr;
+        attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr.val.programmaticStreamSerializationAllowed = 1;
+        const bool pdl = !split && !fresh_plan && chain && !(s->p.flags & IBLB_FLAG_NO_PDL);
+        cfg.attrs = &attr;
+        cfg.numAttrs = pdl ? 1 : 0;
+        IBLB_CUDA(cudaLaunchKernelEx(&cfg, lb_ib_tile_step, bp));
+        s->pdl_chain = !split;
         launches += 1;
-        IBLB_CUDA(cudaGetLastError());
         if (split) {
             q.band = nullptr;
             q.row_begin = s->band_rows;
@@ -208,6 +228,7 @@ int build_graph(iblb_solver *s) {
     const unsigned it0 = s->it;
     const bool stale0 = s->ib_stale;
     unsigned long long dummy = 0;
+    s->pdl_chain = false;
     IBLB_CUDA(cudaStreamBeginCapture(s->stream, cudaStreamCaptureModeThreadLocal));
     int rc = IBLB_OK;
     for (unsigned i = 0; i < kGraphBatch && rc == IBLB_OK; i++)
@@ -271,6 +292,7 @@ int iblb_step(iblb_solver *s, unsigned n_steps) {
     IBLB_CUDA(cudaSetDevice(s->device));
     cudaStream_t st = s->stream;
     unsigned long long launches = 0;
+    s->pdl_chain = false;  // anything may have been enqueued since the last call
     IBLB_CUDA(cudaEventRecord(s->ev0, st));
     const bool coupled = s->connected && !(s->self_left && s->self_right);
     // small grids are launch-bound: replay captured batches of kGraphBatch iterations (captured
@@ -298,6 +320,7 @@ int iblb_step(iblb_solver *s, unsigned n_steps) {
                 left -= kGraphBatch;
                 launches += s->graph_launches;
             }
+            s->pdl_chain = false;  // a batch ends with it_advance
             if (s->p.c_num > 0) {
                 s->ib_stale = fused_path(s);
                 s->kin_base = (long long)s->it - kGraphBatch;

@@ -17,6 +17,7 @@ FLAG_HALF_FORCE_BODY = 1
 FLAG_PICK_HIGHEST_K = 2
 FLAG_NO_GRAPH = 4
 FLAG_NO_FUSE = 8
+FLAG_NO_PDL = 16
 
 IPC_HANDLE_BYTES = 64
 

@@ -44,6 +44,8 @@ extern "C" {
 #define IBLB_FLAG_NO_FUSE 8u         /* keep the immersed-boundary pre-pass as separate kernels
                                         (kinematics, interpolate, spread) instead of the single
                                         fused IB+LB launch per iteration; same results bit for bit */
+#define IBLB_FLAG_NO_PDL 16u         /* no programmatic dependent launch between consecutive fused
+                                        iterations (full kernel-to-kernel serialisation) */
 
 typedef struct iblb_params {
     /* --- the ten driver arguments, main.cu:291-296 --- */

@@ -25,7 +25,7 @@ import pytest
 
 from checkers import (REF_FLAG_HALF_FORCE_BODY, REF_FLAG_PICK_LOWEST_K, Checker, make_params,
                       reference_tau, rel_l2)
-from cuda_iblb_11_b200 import (FLAG_HALF_FORCE_BODY, FLAG_NO_FUSE, FLAG_NO_GRAPH,
+from cuda_iblb_11_b200 import (FLAG_HALF_FORCE_BODY, FLAG_NO_FUSE, FLAG_NO_GRAPH, FLAG_NO_PDL,
                                FLAG_PICK_HIGHEST_K, Params, Solver)
 
 pytestmark = pytest.mark.gpu
@@ -236,17 +236,22 @@ def test_product_against_reference_cuda_golden(name):
 def test_graph_replay_equals_direct_launches():
     a = Solver(Params.channel(288, 192, c_num=6, c_fraction=6))
     b = Solver(Params.channel(288, 192, c_num=6, c_fraction=6, flags=FLAG_NO_GRAPH))
-    for n in (21, 8, 1, 2, 33):
+    c = Solver(Params.channel(288, 192, c_num=6, c_fraction=6, flags=FLAG_NO_GRAPH | FLAG_NO_FUSE))
+    for n in (45, 32, 1, 2, 70):
         a.step(n)
         b.step(n)
-        assert a.it == b.it
-        for x, y in zip(a.fields(), b.fields()):
-            assert np.array_equal(x, y)
-        for x, y in zip(a.markers(), b.markers()):
-            assert np.array_equal(x, y)
-        assert a.Q == b.Q
+        c.step(n)
+        assert a.it == b.it == c.it
+        assert not np.isnan(c.fields()[0]).any()
+        for s in (a, b):
+            for x, y in zip(s.fields(), c.fields()):
+                assert np.array_equal(x, y)
+            for x, y in zip(s.markers(), c.markers()):
+                assert np.array_equal(x, y)
+            assert s.Q == c.Q
     a.close()
     b.close()
+    c.close()
 
 
 @pytest.mark.parametrize("c_num,c_space,c_fraction,Y", [
@@ -263,20 +268,23 @@ def test_fused_single_launch_step_equals_separate_kernels(c_num, c_space, c_frac
     a = Solver(Params.channel(X, Y, **kw))
     b = Solver(Params.channel(X, Y, flags=FLAG_NO_FUSE | FLAG_NO_GRAPH, **kw))
     c = Solver(Params.channel(X, Y, flags=FLAG_NO_GRAPH, **kw))
-    for n in (1, 2, 17, 9):
-        for s in (a, b, c):
+    d = Solver(Params.channel(X, Y, flags=FLAG_NO_PDL, **kw))  # no programmatic dependent launch
+    # 36 iterations: the c_fraction=1 case is unstable in the reference itself (the oracle's
+    # force passes 1e6 at step 42 and overflows at 49); the long stable run is the test above
+    for n in (1, 2, 33):
+        for s in (a, b, c, d):
             s.step(n)
         # one launch an iteration (lb_ib_tile_step) + kinematics batch, tile lists and counter
-        # update once per 8 iterations; three an iteration unfused
-        assert a.last_step_launches <= n + 3 * (n // 8) + 6
+        # update once per 32 iterations; three an iteration unfused
+        assert a.last_step_launches <= n + 3 * (n // 32) + 6
         assert 3 * n <= b.last_step_launches <= 3 * n + n // 8 + 1
         ref = (b.fields(), b.markers(), b.force(), b.populations())
-        for s in (a, c):
+        for s in (a, c, d):
             got = (s.fields(), s.markers(), s.force(), s.populations())
             for x, y in zip(ref[0] + ref[1] + ref[2:], got[0] + got[1] + got[2:]):
                 assert np.array_equal(x, y)
             assert s.Q == b.Q and s.it == b.it
-    for s in (a, b, c):
+    for s in (a, b, c, d):
         s.close()
 
 
