@@ -34,8 +34,32 @@ namespace iblb {
         if (threadIdx.x == 0 && p.dbg)                                                             \
             p.dbg[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 16 + (i)] = clock64();        \
     } while (0)
+__device__ __forceinline__ unsigned long long gtime_ns() {
+    unsigned long long v;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(v));
+    return v;
+}
+// slot i: latest clock64 over the CTA's threads; slot i+2: latest globaltimer
+#define TSTAMP_MAX(i)                                                                              \
+    do {                                                                                           \
+        if (p.dbg) {                                                                               \
+            unsigned long long *d_ = (unsigned long long *)&p.dbg[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 16]; \
+            atomicMax(d_ + (i), (unsigned long long)clock64());                                    \
+            atomicMax(d_ + (i) + 2, gtime_ns());                                                   \
+        }                                                                                          \
+    } while (0)
+// CTA start: thread 0 clears the max slots and notes the global time
+#define TSTAMP_BEGIN()                                                                             \
+    do {                                                                                           \
+        if (threadIdx.x == 0 && p.dbg) {                                                           \
+            long long *d_ = &p.dbg[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 16];         \
+            d_[11] = 0; d_[12] = 0; d_[13] = 0; d_[14] = (long long)gtime_ns();                    \
+        }                                                                                          \
+    } while (0)
 #else
 #define TSTAMP(i)
+#define TSTAMP_MAX(i)
+#define TSTAMP_BEGIN()
 #endif
 
 namespace {
@@ -204,21 +228,40 @@ __device__ __forceinline__ void tile_spread(const TileMarkers &sh, int n, int xg
         // itself adds every marker to every node, zeros included (ImmersedBoundary.cu:194-197)
         const float *__restrict__ wxs = reinterpret_cast<const float *>(sh.wx);
         const float *__restrict__ wys = reinterpret_cast<const float *>(sh.wy);
-        while (mine) {
-            const int q = w * 32 + __ffs(mine) - 1;
+        // software-pipelined: the next hit's shared-memory loads are in flight while the current
+        // one is added, so only the four DADD chains are serial
+        int q = 0, ix = 0, iy = 0;
+        float4 fb = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (mine) {
+            q = w * 32 + __ffs(mine) - 1;
             mine &= mine - 1;
-            const float4 fb = sh.fb[q];
-            const int ix = xg - __float_as_int(fb.z);  // 0..3 for a hit
-            const int iy = y0 - __float_as_int(fb.w);  // row y0; row y0+1 is iy+1; -1..3 for a hit
+            fb = sh.fb[q];
+            ix = xg - __float_as_int(fb.z);  // 0..3 for a hit
+            iy = y0 - __float_as_int(fb.w);  // row y0; row y0+1 is iy+1; -1..3 for a hit
+        } else {
+            continue;
+        }
+        for (;;) {
             const float ddx = wxs[4 * q + ix];
             const float wa = wys[4 * q + max(iy, 0)];
             const float wb = wys[4 * q + min(iy + 1, 3)];
-            const float del0 = iy >= 0 ? ddx * wa : 0.f;
-            const float del1 = iy <= 2 ? ddx * wb : 0.f;
-            fx0 += (double)(fb.x * del0);
-            fy0 += (double)(fb.y * del0);
-            fx1 += (double)(fb.x * del1);
-            fy1 += (double)(fb.y * del1);
+            const float Fx = fb.x, Fy = fb.y;
+            const bool lo = iy >= 0, hi = iy <= 2;
+            const bool more = mine != 0;
+            if (more) {
+                q = w * 32 + __ffs(mine) - 1;
+                mine &= mine - 1;
+                fb = sh.fb[q];
+                ix = xg - __float_as_int(fb.z);
+                iy = y0 - __float_as_int(fb.w);
+            }
+            const float del0 = lo ? ddx * wa : 0.f;
+            const float del1 = hi ? ddx * wb : 0.f;
+            fx0 += (double)(Fx * del0);
+            fy0 += (double)(Fy * del0);
+            fx1 += (double)(Fx * del1);
+            fy1 += (double)(Fy * del1);
+            if (!more) break;
         }
     }
 }
@@ -348,6 +391,7 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
     const bool active = x < L.W;  // warp-uniform
     const bool band_tile = ty0 < p.band_rows;  // block-uniform
     TSTAMP(0);
+    TSTAMP_BEGIN();
 
     // Programmatic dependent launch: the next iteration's CTAs may start as soon as every CTA of
     // this one is running.  Everything up to pdl_wait() reads only the prescribed marker data (the
@@ -390,15 +434,26 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
     }
     pdl_wait();
     TSTAMP(1);
+#ifdef IBLB_TILE_TIMING
+    if (threadIdx.x == 0 && p.dbg) p.dbg[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 16 + 12] = (long long)gtime_ns();
+#endif
     Pulled q;
     if (active) load_pulled(L, lp.src, x, y0, lane, q);
 #ifdef IBLB_TILE_TIMING
     if (threadIdx.x == 0 && p.dbg) p.dbg[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 16 + 15] = n;
 #endif
 
+    // the support nodes in the two rings around the tile: the first 256 are pulled into registers
+    // now and turned into moments after this thread's own nodes, so that their latency overlaps
+    double rf[9];
+    bool rvalid = false;
+    int rc0 = 0;
+    if (t < nring) {
+        rc0 = ring_cell(r0);
+        const int lx = rc0 / kTabY, ly = rc0 - lx * kTabY;
+        rvalid = support_node_pull(L, lp.src, tx0 + L.x0 - 2 + lx, ty0 - 2 + ly, rf);
+    }
     if (n > 0) {
-        // the support nodes in the two rings around the tile
-        if (t < nring) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, ring_cell(r0));
         if (t + 256 < nring) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, ring_cell(r1));
         if (!active) {  // columns past the channel (W % 8 != 0): as the reference would address them
             const int c = (warp + 2) * kTabY + 2 * lane + 2;
@@ -421,6 +476,13 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
             if (own & 1) node_moments(a, sh.rho[c], sh.ux[c], sh.uy[c]);
             if (own & 2) node_moments(b, sh.rho[c + 1], sh.ux[c + 1], sh.uy[c + 1]);
         }
+        if (t < nring) {
+            double rho = 0., ux = 0., uy = 0.;
+            if (rvalid) node_moments(rf, rho, ux, uy);
+            sh.rho[rc0] = rho;
+            sh.ux[rc0] = ux;
+            sh.uy[rc0] = uy;
+        }
         TSTAMP(4);
         __syncthreads();
         TSTAMP(5);
@@ -441,6 +503,7 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
     TSTAMP(9);
     store_pair(lp, x, y0, a, b);
     TSTAMP(10);
+    TSTAMP_MAX(11);
 
     // flux through x = XDIM-5 (ImmersedBoundary.cu:259-264), same slots and order as lb_fused_v2
     if (x == lp.xq && lp.qacc != nullptr) {

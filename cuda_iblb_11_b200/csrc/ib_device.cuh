@@ -94,9 +94,8 @@ __device__ __forceinline__ float delta_1d(float r) {
 // (0, y+1).  The node's nine populations are pulled out of the post-collision buffer `src` (pull
 // form of LatticeBoltzmann.cu:173-373 incl. the wall rules).  False when j lies outside the array
 // or the node's source columns are not held by this slab: such a node contributes nothing.
-__device__ __forceinline__ bool support_node_moments(const Lattice &L,
-                                                     const double *__restrict__ src, int x, int y,
-                                                     double &rho, double &ux, double &uy) {
+__device__ __forceinline__ bool support_node_pull(const Lattice &L, const double *__restrict__ src,
+                                                  int x, int y, double (&f)[9]) {
     const long long j = (long long)y * L.XDIM + x;
     if (j < 0 || j >= (long long)L.XDIM * L.YDIM) return false;
     int ya = y, xa = x;
@@ -109,7 +108,6 @@ __device__ __forceinline__ bool support_node_moments(const Lattice &L,
     if (xl < -(L.G - 1)) xl += L.XDIM;
     else if (xl > L.W + L.G - 2) xl -= L.XDIM;
     if (xl < -(L.G - 1) || xl > L.W + L.G - 2) return false;
-    double f[9];
 #pragma unroll
     for (int q = 0; q < 9; q++) {
         int pi = q, xsrc = xl - kCx[q], ysrc = ya - kCy[q];
@@ -122,6 +120,14 @@ __device__ __forceinline__ bool support_node_moments(const Lattice &L,
         }
         f[q] = src[pi * L.plane + L.off(xsrc, ysrc)];
     }
+    return true;
+}
+
+__device__ __forceinline__ bool support_node_moments(const Lattice &L,
+                                                     const double *__restrict__ src, int x, int y,
+                                                     double &rho, double &ux, double &uy) {
+    double f[9];
+    if (!support_node_pull(L, src, x, y, f)) return false;
     rho = f[0] + f[1] + f[2] + f[3] + f[4] + f[5] + f[6] + f[7] + f[8];
     ux = (f[1] - f[3] + f[5] - f[6] - f[7] + f[8]) / rho;
     uy = (f[2] - f[4] + f[5] + f[6] - f[7] - f[8]) / rho;

@@ -307,16 +307,35 @@ int iblb_destroy(iblb_solver *s) {
         std::vector<long long> h(nc * 16);
         cudaMemcpy(h.data(), s->dbg_dev, sizeof(long long) * nc * 16, cudaMemcpyDeviceToHost);
         size_t worst = 0;
-        double avg[11] = {0};
+        // slots: 0..10 clock64 of thread 0 at the phase boundaries, 11 latest clock64 at exit over
+        // the CTA's threads, 12 globaltimer at wait return, 13 latest globaltimer at exit,
+        // 14 globaltimer at CTA start, 15 markers of the tile
+        double avg[12] = {0};
         for (size_t c = 0; c < nc; c++) {
-            if (h[c * 16 + 10] - h[c * 16] > h[worst * 16 + 10] - h[worst * 16]) worst = c;
-            for (int i = 1; i <= 10; i++) avg[i] += (double)(h[c * 16 + i] - h[c * 16]) / nc;
+            if (h[c * 16 + 13] - h[c * 16 + 12] > h[worst * 16 + 13] - h[worst * 16 + 12]) worst = c;
+            for (int i = 1; i <= 11; i++) avg[i] += (double)(h[c * 16 + i] - h[c * 16]) / nc;
         }
         fprintf(stderr, "tile timing (%zu CTAs), cycles since CTA start: avg", nc);
-        for (int i = 1; i <= 10; i++) fprintf(stderr, " %.0f", avg[i]);
-        fprintf(stderr, "\n  worst CTA %zu (n=%lld):", worst, h[worst * 16 + 15]);
-        for (int i = 1; i <= 10; i++) fprintf(stderr, " %lld", h[worst * 16 + i] - h[worst * 16]);
-        fprintf(stderr, "\n");
+        for (int i = 1; i <= 11; i++) fprintf(stderr, " %.0f", avg[i]);
+        fprintf(stderr, "\n  longest CTA after the wait %zu (n=%lld):", worst, h[worst * 16 + 15]);
+        for (int i = 1; i <= 11; i++) fprintf(stderr, " %lld", h[worst * 16 + i] - h[worst * 16]);
+        long long t0 = h[14], tw0 = h[12], tw1 = 0, t1 = 0;
+        for (size_t c = 0; c < nc; c++) {
+            if (h[c * 16 + 14] < t0) t0 = h[c * 16 + 14];
+            if (h[c * 16 + 12] < tw0) tw0 = h[c * 16 + 12];
+            if (h[c * 16 + 12] > tw1) tw1 = h[c * 16 + 12];
+            if (h[c * 16 + 13] > t1) t1 = h[c * 16 + 13];
+        }
+        double a0 = 0, a1 = 0; int c0n = 0, c1n = 0; long long m0 = 0, m1 = 0;
+        for (size_t c = 0; c < nc; c++) {
+            const long long d = h[c * 16 + 13] - h[c * 16 + 12];
+            if (h[c * 16 + 15] > 0) { a1 += d; c1n++; if (d > m1) m1 = d; }
+            else { a0 += d; c0n++; if (d > m0) m0 = d; }
+        }
+        fprintf(stderr, "\n  ns from wait return to last thread exit: %d tiles without markers avg %.0f max %lld, %d with markers avg %.0f max %lld",
+                c0n, c0n ? a0 / c0n : 0., m0, c1n, c1n ? a1 / c1n : 0., m1);
+        fprintf(stderr, "\n  grid, ns since the first CTA start: wait returns %lld..%lld, last exit %lld\n",
+                tw0 - t0, tw1 - t0, t1 - t0);
         cudaFree(s->dbg_dev);
     }
 #endif
