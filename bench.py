@@ -201,13 +201,15 @@ def run_ours(a):
     pl = Plumbing(a.gpus)
     n = max(1, a.gpus)
     s, p, nodes_total, nodes_local = make_solver(pl, a.workload, n)
-    s.step(a.warmup)
-    s.sync()
-    pl.barrier()
     sampler = ClockSampler(pl.local)
     if pl.rank == 0:
         sampler.start()
         time.sleep(0.25)
+    # warm-up right before the timed region (an idle GPU drops its clocks within a fraction of a
+    # second, which would otherwise be billed to the first timed steps)
+    s.step(a.warmup)
+    s.sync()
+    pl.barrier()
     # ---- timed region: K steps, device time by CUDA events on the solver's stream ----
     pl.barrier()
     s.sync()
@@ -340,10 +342,10 @@ def run_reference(a):
     steps, warm = a.steps, a.warmup
     if kind != "ref_cuda":
         steps, warm = min(steps, 3), 1
-    c.step(warm)
     sampler = ClockSampler(local)
     sampler.start()
     time.sleep(0.25)
+    c.step(warm)
     t0 = time.time()
     c.step(steps)
     t = c.last_step_seconds
