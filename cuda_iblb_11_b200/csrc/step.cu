@@ -77,7 +77,7 @@ int launch_lb(iblb_solver *s, const LbParams &q, cudaStream_t st, unsigned long 
 //   whole channel on this GPU:  lb_ib_tile_step: ONE launch (2 on tall grids, where lb_fused_v2
 //                               takes the rows above the force band), plus, once per kKinBatch
 //                               iterations, ib_kinematics_batch + ib_tile_lists
-//   x-slab coupled to others:   [slab wait] -> ib_markers -> ib_spread -> lb_fused_v2 on the
+//   x-slab coupled to others:   [slab wait] -> ib_kinematics_batch (1 in 32) -> ib_interp -> ib_spread -> lb_fused_v2 on the
 //                               boundary columns -> signal -> lb_fused_v2 on the interior
 // `pe`: time the phases separately (markers / spread / LB), which forces the unfused chain.
 int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEvents *pe,
