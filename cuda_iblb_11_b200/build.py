@@ -14,7 +14,7 @@ LIB = os.path.join(PKG, "libiblb.so")
 APP = os.path.join(ROOT, "app")
 
 CUDA_SOURCES = ["lb_kernels.cu", "ib_kernels.cu", "fused_step.cu", "solver.cu", "step.cu",
-                "slab.cu"]
+                "slab.cu", "checkpoint.cu"]
 HOST_SOURCES = ["params.cpp", "run.cpp"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 

@@ -69,8 +69,16 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
                   "x" + to_string_3(p.T_pow) + "-flux.dat";
     string parameters = raw_data + "/SimLog.txt";
 
+    // checkpoint / restart (extension; environment only, the argv surface stays the reference's):
+    //   IBLB_CHECKPOINT=<file>  written after every output interval and at the end of the run
+    //   IBLB_RESTART=<file>     continue from it: the flux file is appended to, not truncated
+    const char *ckpt_path = getenv("IBLB_CHECKPOINT");
+    const char *restart_path = getenv("IBLB_RESTART");
+    if (ckpt_path && !*ckpt_path) ckpt_path = nullptr;
+    if (restart_path && !*restart_path) restart_path = nullptr;
+
     ofstream fsA, fsB, fsC;
-    fsB.open(flux.c_str(), ofstream::trunc);
+    fsB.open(flux.c_str(), restart_path ? ofstream::app : ofstream::trunc);
     if (!fsB) {
         iblb::set_error("cannot write " + flux);
         return IBLB_EIO;
@@ -86,6 +94,15 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
     iblb_solver *s = nullptr;
     int rc = iblb_create(&p, &s);
     if (rc) return rc;
+    if (restart_path) {
+        rc = iblb_load_checkpoint(s, restart_path);
+        if (rc) {
+            string keep = iblb_last_error();
+            iblb_destroy(s);
+            iblb::set_error(keep);
+            return rc;
+        }
+    }
 
     // ---- SimLog header, main.cu:761-790 ----
     const double l_0 = 0.000006, t_0 = 0.067;
@@ -121,7 +138,7 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
 
     // iteration `it` (0-based) is complete after it+1 steps; outputs follow iterations with
     // it % INTERVAL == 0 (main.cu:938); everything in between runs without host involvement
-    unsigned done = 0;
+    unsigned done = iblb_iteration(s);  // 0, or where the checkpoint was taken
     while (done < ITERATIONS && rc == IBLB_OK) {
         unsigned it_out;  // next iteration index whose completion triggers output
         if (INTERVAL == 0) it_out = ITERATIONS;  // no periodic output
@@ -166,6 +183,7 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
             fsB << it * p.t_scale << "\t" << Q * p.x_scale << endl;  // main.cu:1002
             fsB.close();
         }
+        if (ckpt_path && (rc = iblb_save_checkpoint(s, ckpt_path)) != IBLB_OK) break;
         if (it == INTERVAL && INTERVAL != 0) {  // main.cu:1007-1022
             const double cycle = now_seconds();
             time_t p_runtime = (time_t)((cycle - start) * (ITERATIONS / INTERVAL));

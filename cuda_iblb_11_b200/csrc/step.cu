@@ -255,7 +255,17 @@ int build_graph(iblb_solver *s) {
 // somebody asks for them
 int materialise_ib(iblb_solver *s) {
     if (!s->ib_stale || s->p.c_num == 0 || s->it == 0) return IBLB_OK;
-    IbParams ib = make_ib_params(s, s->cur ^ 1, (int)((long long)s->it - 1 - s->kin_base));
+    const long long last = (long long)s->it - 1;
+    if (s->kin_base < 0 || last < s->kin_base || last >= s->kin_base + kKinBatch) {
+        // the marker slots do not hold the last iteration (right after iblb_load_checkpoint)
+        IbParams kp = make_ib_params(s, s->cur ^ 1, 0);
+        kp.it = (int)last;
+        ib_kinematics_batch<<<dim3(kp.c_num, kKinBatch), 1024, 0, s->stream>>>(kp);
+        IBLB_CUDA(cudaGetLastError());
+        s->kin_base = last;
+        s->lists_base = -1;
+    }
+    IbParams ib = make_ib_params(s, s->cur ^ 1, (int)(last - s->kin_base));
     ib_interp<<<(ib.Ns + 23) / 24, 256, 0, s->stream>>>(ib);
     IBLB_CUDA(cudaGetLastError());
     dim3 g((s->L.W + kSpreadTileX - 1) / kSpreadTileX, s->band_rows / kSpreadTileY);

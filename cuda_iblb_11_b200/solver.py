@@ -97,6 +97,7 @@ SYMBOLS = [
     "iblb_set_fields", "iblb_marker_fine_index", "iblb_last_step_seconds",
     "iblb_last_step_launches", "iblb_profile_phases", "iblb_export_halo", "iblb_connect",
     "iblb_connect_local", "iblb_halo_ptrs", "iblb_run", "iblb_last_error", "iblb_version",
+    "iblb_save_checkpoint", "iblb_load_checkpoint",
 ]
 
 
@@ -129,6 +130,8 @@ def lib():
     L.iblb_get_markers.argtypes = [vp, vp, vp, vp, vp]
     L.iblb_get_flux.argtypes = [vp, dp]
     L.iblb_set_fields.argtypes = [vp, vp, vp]
+    L.iblb_save_checkpoint.argtypes = [vp, ctypes.c_char_p]
+    L.iblb_load_checkpoint.argtypes = [vp, ctypes.c_char_p]
     L.iblb_marker_fine_index.argtypes = [vp, ctypes.c_uint]
     L.iblb_last_step_seconds.argtypes = [vp, dp]
     L.iblb_last_step_launches.argtypes = [vp, ctypes.POINTER(ctypes.c_ulonglong)]
@@ -208,6 +211,14 @@ class Solver:
         u = np.ascontiguousarray(u, np.float64)
         assert rho.size == self.size and u.size == 2 * self.size
         _check(lib().iblb_set_fields(self._h, rho.ctypes.data, u.ctypes.data))
+
+    def save_checkpoint(self, path):
+        """Complete time-stepping state to `path` (iblb_save_checkpoint)."""
+        _check(lib().iblb_save_checkpoint(self._h, os.fsencode(path)))
+
+    def load_checkpoint(self, path):
+        """State of a solver with the same parameters from `path` (iblb_load_checkpoint)."""
+        _check(lib().iblb_load_checkpoint(self._h, os.fsencode(path)))
 
     def marker_fine_index(self, j):
         return lib().iblb_marker_fine_index(self._h, j)

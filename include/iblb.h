@@ -148,6 +148,14 @@ int iblb_halo_ptrs(iblb_solver *s, int face, void **send, void **recv, size_t *b
                    size_t *pop_stride_bytes);
 /* In staged mode iblb_step(1) must be followed by an exchange before the next step. */
 
+/* Checkpoint / restart (new; the reference restarts its 100 000-step runs from scratch).  The file
+ * holds the complete time-stepping state of this solver (both population buffers, iteration,
+ * flux sums); marker state is a function of the iteration and is not stored.  Load into a solver
+ * created with the same parameters (flags may differ), before iblb_connect for x-slabs; stepping
+ * on and every getter then continue bit for bit as if the run had never stopped. */
+int iblb_save_checkpoint(iblb_solver *s, const char *path);
+int iblb_load_checkpoint(iblb_solver *s, const char *path);
+
 /* ---- driver-level run (replaces main() as a whole: SimLog, flux, fluid/cilia files) ------ */
 /* Runs ITERATIONS steps writing the reference's Data/ tree under `root` (NULL: "Data/").
  * main.cu:589-631, 758-790, 936-1005, 1030-1060. */

@@ -124,6 +124,75 @@ def test_set_fields_round_trip_and_restart():
     s.close()
 
 
+def _state(s):
+    return s.fields() + s.markers() + (s.force(), s.populations(), np.array([s.Q, s.it]))
+
+
+@pytest.mark.parametrize("kw,flags_b", [
+    (dict(c_num=6, c_fraction=6), FLAG_NO_GRAPH),             # C1, restart under direct launches
+    (dict(c_num=6, c_fraction=6), FLAG_NO_FUSE),              # ... and under the unfused chain
+    (dict(c_num=0, gx=1e-6), 0),                              # forced pure LB
+])
+def test_checkpoint_restart_continues_bit_for_bit(tmp_path, kw, flags_b):
+    """iblb_save_checkpoint / iblb_load_checkpoint: a solver restarted from
+    the file answers every getter as the original did when the file was written, and after the
+    same further steps holds the same state, bit for bit (flux sum included)."""
+    path = str(tmp_path / "state.ckp")
+    a = Solver(Params.channel(288, 192, **kw))
+    a.step(45)
+    at_save = _state(a)
+    a.save_checkpoint(path)
+    a.step(50)
+    later = _state(a)
+    a.close()
+    b = Solver(Params.channel(288, 192, flags=flags_b, **kw))
+    b.step(3)  # whatever it held is replaced
+    b.load_checkpoint(path)
+    assert b.it == 45
+    for x, y in zip(_state(b), at_save):
+        assert np.array_equal(x, y)
+    b.step(50)
+    for x, y in zip(_state(b), later):
+        assert np.array_equal(x, y)
+    # second generation: checkpoint of the restarted run, loaded before any getter was called
+    b.save_checkpoint(path)
+    b.close()
+    c = Solver(Params.channel(288, 192, **kw))
+    c.load_checkpoint(path)
+    c.step(7)
+    a2 = Solver(Params.channel(288, 192, **kw))
+    a2.step(102)
+    for x, y in zip(_state(c), _state(a2)):
+        assert np.array_equal(x, y)
+    c.close()
+    a2.close()
+
+
+def test_checkpoint_rejects_foreign_and_damaged_files(tmp_path):
+    path = str(tmp_path / "state.ckp")
+    a = Solver(Params.channel(288, 192, c_num=6, c_fraction=6))
+    a.step(5)
+    a.save_checkpoint(path)
+    other = Solver(Params.channel(288, 192, c_num=6, c_fraction=3))
+    with pytest.raises(Exception, match="other parameters"):
+        other.load_checkpoint(path)
+    other.close()
+    blob = open(path, "rb").read()
+    short = str(tmp_path / "short.ckp")
+    open(short, "wb").write(blob[:len(blob) // 2])
+    with pytest.raises(Exception, match="truncated"):
+        a.load_checkpoint(short)
+    junk = str(tmp_path / "junk.ckp")
+    open(junk, "wb").write(b"not a checkpoint" * 64)
+    with pytest.raises(Exception, match="IBLBCKP1"):
+        a.load_checkpoint(junk)
+    with pytest.raises(Exception, match="cannot open"):
+        a.load_checkpoint(str(tmp_path / "missing.ckp"))
+    a.load_checkpoint(path)  # still usable after the failures
+    assert a.it == 5
+    a.close()
+
+
 # ------------------------------------------------------------------------------ IB-coupled
 def test_cilia6_first_line_matches_oracle():
     """`./app 1 6 48 1.0 1.0 5 1.0 100 S B` (cilia6.sh:7).  The reference's coupling is unstable for

@@ -210,6 +210,32 @@ def test_run_writes_the_reference_data_tree(tmp_path):
     assert int(v[4]) == eps[k]
 
 
+def test_run_restarts_from_a_checkpoint(tmp_path, monkeypatch):
+    """Driver level: IBLB_CHECKPOINT / IBLB_RESTART around iblb_run.  A 41-iteration run that
+    restarts from the checkpoint a 21-iteration run left writes the same snapshots and the same
+    final flux as the uninterrupted 41-iteration run."""
+    def params(iterations):
+        p = Params.from_args("6 6 48 1.0 1.0 5 1.0 100 0 1".split())
+        p.ITERATIONS, p.INTERVAL, p.device = iterations, 20, 0
+        return p
+    full, part = str(tmp_path / "full"), str(tmp_path / "part")
+    run(params(41), full)
+    ck = str(tmp_path / "run.ckp")
+    monkeypatch.setenv("IBLB_CHECKPOINT", ck)
+    run(params(21), part)
+    monkeypatch.delenv("IBLB_CHECKPOINT")
+    monkeypatch.setenv("IBLB_RESTART", ck)
+    run(params(41), part)
+    monkeypatch.delenv("IBLB_RESTART")
+    for sub, name in (("Raw/6/6", "40-fluid.dat"), ("Cilia/6/6", "40-cilia.dat"),
+                      ("Raw/6/6", "20-fluid.dat")):
+        assert open(os.path.join(full, sub, name)).read() == open(os.path.join(part, sub, name)).read()
+    fa = open(os.path.join(full, "Flux", "6_6_48_1_1x5-flux.dat")).read().splitlines()
+    fb = open(os.path.join(part, "Flux", "6_6_48_1_1x5-flux.dat")).read().splitlines()
+    assert fb[:2] == fa[:2] and fb[-2:] == fa[-2:]  # it 0, 20 ... 40, end-of-run line
+
+
+
 def test_app_executable_surface(tmp_path):
     app = os.path.join(ROOT, "app")
     if not os.path.exists(app):
