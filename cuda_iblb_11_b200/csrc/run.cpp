@@ -7,7 +7,13 @@
 
 #include <chrono>
 #include <cmath>
+#include <condition_variable>
 #include <cstdlib>
+#include <deque>
+#include <functional>
+#include <memory>
+#include <mutex>
+#include <thread>
 #include <ctime>
 #include <fstream>
 #include <iomanip>
@@ -45,6 +51,62 @@ double now_seconds() {
         .count();
 }
 
+// one fluid + cilia snapshot on its way to the text files
+struct Snapshot {
+    std::vector<double> rho, u;
+    std::vector<float> sm, us;
+    std::vector<int> eps;
+};
+
+// Writer thread: the reference formats and flushes one line per node on the
+// thread that drives the GPU (main.cu:954-994, `endl` per line), so BigData=1 stalls its time loop
+// for the whole write.  Here the loop hands the snapshot over and steps on; at most two snapshots
+// are in flight (submit blocks beyond that), files appear in iteration order.
+class SnapshotWriter {
+  public:
+    SnapshotWriter() : ok_(true), stop_(false), worker_([this] { loop(); }) {}
+    ~SnapshotWriter() { finish(); }
+    void submit(std::function<bool()> job) {
+        std::unique_lock<std::mutex> lk(m_);
+        cv_.wait(lk, [this] { return jobs_.size() < 2; });
+        jobs_.push_back(std::move(job));
+        cv_.notify_all();
+    }
+    // drain and join; false when any file could not be written
+    bool finish() {
+        {
+            std::unique_lock<std::mutex> lk(m_);
+            stop_ = true;
+            cv_.notify_all();
+        }
+        if (worker_.joinable()) worker_.join();
+        return ok_;
+    }
+
+  private:
+    void loop() {
+        for (;;) {
+            std::function<bool()> job;
+            {
+                std::unique_lock<std::mutex> lk(m_);
+                cv_.wait(lk, [this] { return stop_ || !jobs_.empty(); });
+                if (jobs_.empty()) return;
+                job = jobs_.front();
+            }
+            const bool ok = job();
+            std::unique_lock<std::mutex> lk(m_);
+            if (!ok) ok_ = false;
+            jobs_.pop_front();
+            cv_.notify_all();
+        }
+    }
+    std::mutex m_;
+    std::condition_variable cv_;
+    std::deque<std::function<bool()>> jobs_;
+    bool ok_, stop_;
+    std::thread worker_;
+};
+
 }  // namespace
 
 extern "C" int iblb_run(const iblb_params *pp, const char *root) {
@@ -77,7 +139,7 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
     if (ckpt_path && !*ckpt_path) ckpt_path = nullptr;
     if (restart_path && !*restart_path) restart_path = nullptr;
 
-    ofstream fsA, fsB, fsC;
+    ofstream fsB, fsC;
     fsB.open(flux.c_str(), restart_path ? ofstream::app : ofstream::trunc);
     if (!fsB) {
         iblb::set_error("cannot write " + flux);
@@ -125,16 +187,7 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
     cout << "Running Simulation...\n";
     const double start = now_seconds();
 
-    vector<double> rho, u;
-    vector<float> sm, us;
-    vector<int> eps;
-    if (p.BigData) {
-        rho.resize(size);
-        u.resize(2 * size);
-        sm.resize(2 * (size_t)Ns + 2);
-        us.resize(2 * (size_t)Ns + 2);
-        eps.resize((size_t)Ns + 1);
-    }
+    SnapshotWriter writer;  // BigData text files are written behind the step loop
 
     // iteration `it` (0-based) is complete after it+1 steps; outputs follow iterations with
     // it % INTERVAL == 0 (main.cu:938); everything in between runs without host involvement
@@ -150,31 +203,46 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
         const unsigned it = done - 1;
         if (INTERVAL != 0 && it % INTERVAL == 0) {
             if (p.BigData) {
-                rc = iblb_get_fields(s, rho.data(), u.data());
+                // the state is read back here; formatting and writing the text files (the slow
+                // part: one line per node) happen on the writer thread while the loop steps on
+                auto snap = make_shared<Snapshot>();
+                snap->rho.resize(size);
+                snap->u.resize(2 * size);
+                snap->sm.resize(2 * (size_t)Ns + 2);
+                snap->us.resize(2 * (size_t)Ns + 2);
+                snap->eps.resize((size_t)Ns + 1);
+                rc = iblb_get_fields(s, snap->rho.data(), snap->u.data());
                 if (rc) break;
-                string outfile = raw_data + to_string(it) + "-fluid.dat";
-                fsA.open(outfile.c_str());
-                for (size_t j = 0; j < size; j++) {  // main.cu:958-969
-                    const int x = (int)(j % XDIM);
-                    const int y = (int)((j - j % XDIM) / XDIM);
-                    const double ab = sqrt(u[j] * u[j] + u[size + j] * u[size + j]);
-                    fsA << x * p.x_scale << "\t" << y * p.x_scale << "\t" << u[j] * p.s_scale
-                        << "\t" << u[size + j] * p.s_scale << "\t" << ab * p.s_scale << "\t"
-                        << rho[j] << endl;
-                    if (x == (int)XDIM - 1) fsA << endl;
-                }
-                fsA.close();
-                rc = iblb_get_markers(s, sm.data(), us.data(), nullptr, eps.data());
+                rc = iblb_get_markers(s, snap->sm.data(), snap->us.data(), nullptr, snap->eps.data());
                 if (rc) break;
-                outfile = cilia_data + to_string(it) + "-cilia.dat";
-                fsA.open(outfile.c_str());
-                for (int k = 0; k < Ns; k++) {  // main.cu:986-992
-                    fsA << sm[2 * k + 0] * p.x_scale << "\t" << sm[2 * k + 1] * p.x_scale << "\t"
-                        << us[2 * k + 0] * p.s_scale << "\t" << us[2 * k + 1] * p.s_scale << "\t"
-                        << eps[k] << "\n";
-                    if (k % 96 == 95 || sm[2 * k + 0] > XDIM - 1 || sm[2 * k + 0] < 1) fsA << "\n";
-                }
-                fsA.close();
+                const string fluid_file = raw_data + to_string(it) + "-fluid.dat";
+                const string cilia_file = cilia_data + to_string(it) + "-cilia.dat";
+                const double x_scale = p.x_scale, s_scale = p.s_scale;
+                writer.submit([=]() -> bool {
+                    const vector<double> &rho = snap->rho, &u = snap->u;
+                    const vector<float> &sm = snap->sm, &us = snap->us;
+                    const vector<int> &eps = snap->eps;
+                    ofstream f(fluid_file.c_str());
+                    for (size_t j = 0; j < size; j++) {  // main.cu:958-969
+                        const int x = (int)(j % XDIM);
+                        const int y = (int)((j - j % XDIM) / XDIM);
+                        const double ab = sqrt(u[j] * u[j] + u[size + j] * u[size + j]);
+                        f << x * x_scale << "\t" << y * x_scale << "\t" << u[j] * s_scale << "\t"
+                          << u[size + j] * s_scale << "\t" << ab * s_scale << "\t" << rho[j] << "\n";
+                        if (x == (int)XDIM - 1) f << "\n";
+                    }
+                    f.close();
+                    bool ok = !f.fail();
+                    f.open(cilia_file.c_str());
+                    for (int k = 0; k < Ns; k++) {  // main.cu:986-992
+                        f << sm[2 * k + 0] * x_scale << "\t" << sm[2 * k + 1] * x_scale << "\t"
+                          << us[2 * k + 0] * s_scale << "\t" << us[2 * k + 1] * s_scale << "\t"
+                          << eps[k] << "\n";
+                        if (k % 96 == 95 || sm[2 * k + 0] > XDIM - 1 || sm[2 * k + 0] < 1) f << "\n";
+                    }
+                    f.close();
+                    return ok && !f.fail();
+                });
             }
             double Q = 0.;
             rc = iblb_get_flux(s, &Q);
@@ -193,6 +261,10 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
             fsC << "\nCompletion time: " << asctime(timeinfo) << endl;
             fsC.close();
         }
+    }
+    if (!writer.finish() && rc == IBLB_OK) {
+        iblb::set_error("cannot write the snapshot files under " + output_data);
+        rc = IBLB_EIO;
     }
     if (rc == IBLB_OK) {
         double Q = 0.;
