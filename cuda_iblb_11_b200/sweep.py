@@ -1,0 +1,148 @@
+"""Ensemble launcher for the reference's batch scripts (cilia6.sh, cilia12.sh, multiapp.sh, app.sh).
+
+The reference runs the `./app ...` lines of a script one after the other on one GPU
+(multiapp.sh:7-9, cilia6.sh:7-17).  The runs are independent, so here run i goes to GPU
+i mod N ("replicas only"): one worker process per GPU, each executing its lines in
+script order through `iblb_run` (the whole of main.cu for one line, Data/ tree included), no
+communication.  When all are done the flux curves the runs wrote (main.cu:998-1004,1030-1034) are
+gathered into `<root>/Flux/sweep-summary.tsv`.
+
+    python -m cuda_iblb_11_b200.sweep multiapp.sh --gpus 8 --root Data/
+
+`--iterations K` / `--interval K` shorten every run (smoke tests); the default is what each line asks
+for.  The worker needs a GPU and libiblb.so; planning and the summary do not.
+"""
+import argparse
+import multiprocessing as mp
+import os
+import sys
+import time
+
+from .slabs import assign_runs, parse_sweep_script
+
+
+def plan(script_text, n_gpus):
+    """[(gpu, run index, argv words)] in execution order per GPU."""
+    runs = parse_sweep_script(script_text)
+    out = []
+    for gpu, idxs in enumerate(assign_runs(len(runs), n_gpus)):
+        out += [(gpu, i, runs[i]) for i in idxs]
+    return runs, out
+
+
+def flux_file_name(p):
+    """Name of the flux file of a run, main.cu:612 (`to_string_3`: three significant digits)."""
+    def s3(v):
+        return "%.3g" % v
+    return "%d_%d_%d_%s_%sx%d-flux.dat" % (p.c_fraction, p.c_num, p.c_space, s3(p.Re),
+                                           s3(p.T_num), p.T_pow)
+
+
+def read_flux(path):
+    """[(t, Q)] of a flux file: `it*t_scale \\t Q*x_scale` per line."""
+    rows = []
+    with open(path) as f:
+        for line in f:
+            w = line.split()
+            if len(w) == 2:
+                rows.append((float(w[0]), float(w[1])))
+    return rows
+
+
+def _worker(gpu, jobs, root, iterations, interval, q):
+    from .solver import Params, run  # loads libiblb.so; fails loudly when it is missing
+    for idx, words in jobs:
+        t0 = time.time()
+        try:
+            p = Params.from_args(words)
+            p.device = gpu
+            if iterations:
+                p.ITERATIONS = iterations
+            if interval is not None:
+                p.INTERVAL = interval
+            run(p, root)
+            nodes = int(p.XDIM) * int(p.YDIM)
+            q.put((idx, gpu, None, flux_file_name(p), nodes * int(p.ITERATIONS), time.time() - t0))
+        except Exception as e:  # reported, the other runs of this GPU go on
+            q.put((idx, gpu, "%s: %s" % (type(e).__name__, e), None, 0, time.time() - t0))
+
+
+def run_sweep(script_text, n_gpus=1, root="Data/", iterations=0, interval=None):
+    """Run every `./app` line of the script, spread over n_gpus.  Returns the summary rows:
+    dict(run, gpu, args, error, final_t, final_Q, points, seconds, mlups)."""
+    runs, order = plan(script_text, n_gpus)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = []
+    for gpu in range(n_gpus):
+        jobs = [(i, w) for g, i, w in order if g == gpu]
+        if jobs:
+            pr = ctx.Process(target=_worker, args=(gpu, jobs, root, iterations, interval, q))
+            pr.start()
+            procs.append(pr)
+    results = {}
+    while len(results) < len(runs):
+        try:
+            r = q.get(timeout=1.0)
+            results[r[0]] = r
+        except Exception:
+            if not any(pr.is_alive() for pr in procs) and q.empty():
+                break
+    for pr in procs:
+        pr.join()
+    rows = []
+    for i, words in enumerate(runs):
+        r = results.get(i)
+        row = dict(run=i, gpu=None, args=" ".join(words), error="worker died", final_t=None,
+                   final_Q=None, points=0, seconds=None, mlups=None)
+        if r is not None:
+            _, gpu, err, fname, updates, secs = r
+            row.update(gpu=gpu, error=err, seconds=secs)
+            if err is None:
+                curve = read_flux(os.path.join(root, "Flux", fname))
+                row.update(points=len(curve), mlups=updates / secs / 1e6 if secs > 0 else None)
+                if curve:
+                    row.update(final_t=curve[-1][0], final_Q=curve[-1][1])
+        rows.append(row)
+    write_summary(rows, os.path.join(root, "Flux", "sweep-summary.tsv"))
+    return rows
+
+
+def write_summary(rows, path):
+    os.makedirs(os.path.dirname(path), exist_ok=True)
+    with open(path, "w") as f:
+        f.write("run\tgpu\targs\tfinal_t\tfinal_Q\tpoints\tseconds\tMLUPS\terror\n")
+        for r in rows:
+            f.write("\t".join(str(r[k]) if r[k] is not None else "" for k in
+                              ("run", "gpu", "args", "final_t", "final_Q", "points", "seconds",
+                               "mlups", "error")) + "\n")
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(description=__doc__.split("\n")[0])
+    ap.add_argument("script", help="a reference batch script (lines starting with ./app)")
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--root", default="Data/")
+    ap.add_argument("--iterations", type=int, default=0, help="override ITERATIONS of every run")
+    ap.add_argument("--interval", type=int, default=None, help="override INTERVAL of every run")
+    ap.add_argument("--dry-run", action="store_true", help="print the assignment and exit")
+    a = ap.parse_args(argv)
+    text = open(a.script).read()
+    runs, order = plan(text, a.gpus)
+    if not runs:
+        print("no ./app lines in %s" % a.script, file=sys.stderr)
+        return 1
+    if a.dry_run:
+        for gpu, i, words in order:
+            print("gpu %d: run %d: ./app %s" % (gpu, i, " ".join(words)))
+        return 0
+    rows = run_sweep(text, a.gpus, a.root, a.iterations, a.interval)
+    bad = [r for r in rows if r["error"]]
+    for r in rows:
+        print("run %(run)d gpu %(gpu)s: %(args)s -> Q %(final_Q)s at t %(final_t)s, "
+              "%(seconds)s s %(error)s" % {**r, "error": r["error"] or ""})
+    return 1 if bad else 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

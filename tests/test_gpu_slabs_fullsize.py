@@ -250,3 +250,23 @@ def test_app_executable_surface(tmp_path):
     assert r.returncode == 0, r.stderr
     assert "Running Simulation..." in r.stdout
     assert os.path.exists(str(tmp_path / "D" / "Flux" / "1_6_48_1_1x5-flux.dat"))
+
+
+def test_sweep_launcher_runs_a_script_and_gathers_the_flux_curves(tmp_path):
+    """cuda_iblb_11_b200.sweep (config C5): the `./app` lines of a multiapp.sh-style script run as
+    independent replicas (worker process per GPU) and give the flux of stand-alone runs."""
+    from cuda_iblb_11_b200 import sweep
+    script = ("#! /bin/bash -l\nmodule load libs/CUDA/8.0.44/binary\n\n"
+              "./app 6 6 1.0 100000 100000 100 0 0\n\n./app 3 6 1.0 100000 100000 100 0 0\n")
+    root = str(tmp_path / "Data")
+    rows = sweep.run_sweep(script, n_gpus=1, root=root, iterations=41, interval=20)
+    assert [r["error"] for r in rows] == [None, None]
+    assert [r["points"] for r in rows] == [4, 4] and all(r["gpu"] == 0 for r in rows)
+    for r, cf in zip(rows, (6, 3)):
+        s = Solver(Params.channel(288, 192, c_num=6, c_fraction=cf))
+        s.step(41)
+        assert r["final_Q"] == pytest.approx(s.Q * 0.0625, rel=2e-5, abs=1e-12)
+        s.close()
+    table = open(os.path.join(root, "Flux", "sweep-summary.tsv")).read().splitlines()
+    assert len(table) == 3 and table[1].split("\t")[2] == "6 6 1.0 100000 100000 100 0 0"
+

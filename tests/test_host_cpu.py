@@ -162,6 +162,37 @@ def test_sweep_script_parsing_and_assignment():
     assert slabs.assign_runs(6, 4) == [[0, 4], [1, 5], [2], [3]]
 
 
+def test_sweep_launcher_plan_names_and_summary(tmp_path, capsys):
+    """cuda_iblb_11_b200.sweep: assignment of a script's lines to GPUs, flux-file names
+    (main.cu:612), flux-curve reader and the summary table; no GPU involved."""
+    from cuda_iblb_11_b200 import sweep
+    runs, order = sweep.plan(CILIA6_SH, 2)
+    assert len(runs) == 3
+    assert [(g, i) for g, i, _ in order] == [(0, 0), (0, 2), (1, 1)]
+    p = Params.from_args(runs[1])
+    assert sweep.flux_file_name(p) == "2_6_48_1_1x5-flux.dat"
+    p = Params.from_args("6 12 48 0.5 2.5 4 1.0 100 0 0".split())
+    assert sweep.flux_file_name(p) == "6_12_48_0.5_2.5x4-flux.dat"
+    f = tmp_path / "x-flux.dat"
+    f.write_text("0\t0\n0.0134\t1.25e-05\n\n0.0268\t2.5e-05\n")
+    assert sweep.read_flux(str(f)) == [(0.0, 0.0), (0.0134, 1.25e-05), (0.0268, 2.5e-05)]
+    rows = [dict(run=0, gpu=1, args="1 6", error=None, final_t=0.02, final_Q=1e-5, points=3,
+                 seconds=1.5, mlups=10.0),
+            dict(run=1, gpu=None, args="2 6", error="worker died", final_t=None, final_Q=None,
+                 points=0, seconds=None, mlups=None)]
+    out = tmp_path / "Flux" / "sweep-summary.tsv"
+    sweep.write_summary(rows, str(out))
+    lines = out.read_text().splitlines()
+    assert lines[0].split("\t") == ["run", "gpu", "args", "final_t", "final_Q", "points", "seconds",
+                                    "MLUPS", "error"]
+    assert lines[1].split("\t") == ["0", "1", "1 6", "0.02", "1e-05", "3", "1.5", "10.0", ""]
+    assert lines[2].split("\t")[8] == "worker died"
+    script = tmp_path / "s.sh"
+    script.write_text(CILIA6_SH)
+    assert sweep.main([str(script), "--gpus", "8", "--dry-run"]) == 0
+    assert "gpu 2: run 2: ./app 3 6 1.0 100000 100000 100 1 0" in capsys.readouterr().out
+
+
 def test_product_package_never_touches_the_oracle():
     pkg = os.path.join(ROOT, "cuda_iblb_11_b200")
     for dirpath, _, files in os.walk(pkg):
