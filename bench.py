@@ -256,7 +256,11 @@ def run_ours(a):
     lb_launches_per_rank = a.steps * (1 if n == 1 or WORKLOADS[a.workload]["scaling"] == "replicas" else 2)
     achieved = BYTES_PER_LUP * (nodes_total / n) * a.steps / t_dev / 1e9
     tr = ncu_traffic()
-    roof = {"bound": "hbm", "kernel": "lb_fused_v2", "achieved": round(achieved, 1),
+    # (whole channel with cilia on one GPU, short grid: the single-launch IB+LB kernel instead)
+    w_ = WORKLOADS[a.workload]
+    whole = n == 1 or w_["scaling"] == "replicas"
+    kernel = "lb_ib_tile_step" if (w_["c_num"] > 0 and whole and w_["Y"] <= 512) else "lb_fused_v2"
+    roof = {"bound": "hbm", "kernel": kernel, "achieved": round(achieved, 1),
             "peak": peak, "peak_source": peak_src, "unit": "GB/s",
             "frac": round(achieved / peak, 4),
             "algorithmic_bytes_per_launch": BYTES_PER_LUP * nodes_local,

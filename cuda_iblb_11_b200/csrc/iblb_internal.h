@@ -68,6 +68,7 @@ struct iblb_solver {
     int *err_dev;
     // flux
     double *qacc, *qpart;
+    double *q_host;            // pinned: nq flux partial sums + the device error flag (one sync)
     int nq;
     bool flux_on;
     int xq_local;

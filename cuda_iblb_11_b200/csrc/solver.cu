@@ -182,6 +182,7 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
     if (rc == IBLB_OK) TRY(cudaMemset(s->buf[1], 0, pop_bytes));
     s->nq = s->vec2 ? (int)p.YDIM / 64 : 1;
     TRY(cudaMalloc((void **)&s->qacc, sizeof(double) * s->nq));
+    TRY(cudaMallocHost((void **)&s->q_host, sizeof(double) * (s->nq + 1)));
     if (!s->vec2) TRY(cudaMalloc((void **)&s->qpart, sizeof(double) * p.YDIM));
     TRY(cudaMalloc((void **)&s->flags, 2 * sizeof(int)));
     if (rc == IBLB_OK) TRY(cudaMemset(s->flags, 0, 2 * sizeof(int)));
@@ -347,6 +348,7 @@ int iblb_destroy(iblb_solver *s) {
         if (s->nb_flag_mapped[f]) cudaIpcCloseMemHandle(s->nb_flag_mapped[f]);
     }
     cudaFree(s->buf[0]); cudaFree(s->buf[1]); cudaFree(s->qacc); cudaFree(s->qpart);
+    if (s->q_host) cudaFreeHost(s->q_host);
     cudaFree(s->flags); cudaFree(s->band); cudaFree(s->M.s); cudaFree(s->M.u_s);
     cudaFree(s->M.F_s); cudaFree(s->M.eps); cudaFree(s->M.bbox); cudaFree(s->coef);
     cudaFree(s->M.wx); cudaFree(s->M.wy); cudaFree(s->M.base);

@@ -480,14 +480,16 @@ int iblb_get_markers(iblb_solver *s, float *pos, float *vel, float *force, int *
 int iblb_get_flux(iblb_solver *s, double *Q) {
     if (!s || !Q) return IBLB_EINVAL;
     IBLB_CUDA(cudaSetDevice(s->device));
-    {
-        int rc = check_device_flag(s);
-        if (rc) return rc;
-    }
-    std::vector<double> part(s->nq);
-    IBLB_CUDA(cudaMemcpyAsync(part.data(), s->qacc, sizeof(double) * s->nq, cudaMemcpyDeviceToHost,
+    // the reference copies Q back every step (main.cu:928): one pinned staging buffer, one sync
+    double *part = s->q_host;
+    int *flag = reinterpret_cast<int *>(s->q_host + s->nq);
+    *flag = 0;
+    IBLB_CUDA(cudaMemcpyAsync(part, s->qacc, sizeof(double) * s->nq, cudaMemcpyDeviceToHost,
                               s->stream));
+    if (s->err_dev)
+        IBLB_CUDA(cudaMemcpyAsync(flag, s->err_dev, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
     IBLB_CUDA(cudaStreamSynchronize(s->stream));
+    if (*flag != 0) return check_device_flag(s);  // sets the message
     double q = 0.;
     for (int i = 0; i < s->nq; i++) q += part[i];  // fixed slot order
     *Q = q;
