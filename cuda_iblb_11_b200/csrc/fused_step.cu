@@ -266,6 +266,65 @@ __device__ __forceinline__ void tile_spread(const TileMarkers &sh, int n, int xg
     }
 }
 
+// Per-thread spreading list, built in the kernel's prologue (before the previous iteration has
+// finished): for the first kSpreadList markers that reach this thread's two nodes, the marker's
+// staged index and the two float delta products (ImmersedBoundary.cu:78) — none of it depends on
+// the fluid.  What is left on the critical path per hit is one F_s load, four float products and
+// the four double adds.  Layout [entry][thread]: conflict-free.
+constexpr int kSpreadList = 12;
+struct SpreadLists {
+    float d0[kSpreadList][256], d1[kSpreadList][256];
+    unsigned short q[kSpreadList][256];
+};
+
+// Moves the lowest hits of this thread out of its masks into the list; returns how many.  The
+// masks keep what did not fit (more than kSpreadList hits): tile_spread adds those afterwards,
+// which preserves the ascending order.
+__device__ __forceinline__ int build_spread_list(const TileMarkers &sh, SpreadLists &sl, int n,
+                                                 int xg, int y0, unsigned (&hit)[kHitWords]) {
+    const int t = threadIdx.x;
+    const float *__restrict__ wxs = reinterpret_cast<const float *>(sh.wx);
+    const float *__restrict__ wys = reinterpret_cast<const float *>(sh.wy);
+    int cnt = 0;
+#pragma unroll
+    for (int w = 0; w < kHitWords; w++) {
+        if (w * 32 >= n) break;
+        unsigned mine = hit[w];
+        while (mine && cnt < kSpreadList) {
+            const int q = w * 32 + __ffs(mine) - 1;
+            mine &= mine - 1;
+            const float4 fb = sh.fb[q];
+            const int ix = xg - __float_as_int(fb.z);  // 0..3 for a hit
+            const int iy = y0 - __float_as_int(fb.w);  // row y0; row y0+1 is iy+1; -1..3 for a hit
+            const float ddx = wxs[4 * q + ix];
+            const float wa = wys[4 * q + max(iy, 0)];
+            const float wb = wys[4 * q + min(iy + 1, 3)];
+            sl.d0[cnt][t] = iy >= 0 ? ddx * wa : 0.f;
+            sl.d1[cnt][t] = iy <= 2 ? ddx * wb : 0.f;
+            sl.q[cnt][t] = (unsigned short)q;
+            cnt++;
+        }
+        hit[w] = mine;
+    }
+    return cnt;
+}
+
+// the listed part of the spreading sum (see tile_spread for the arithmetic)
+__device__ __forceinline__ void list_spread(const TileMarkers &sh, const SpreadLists &sl, int cnt,
+                                            double &fx0, double &fy0, double &fx1, double &fy1) {
+    const int t = threadIdx.x;
+    const float2 *__restrict__ fs = reinterpret_cast<const float2 *>(sh.fb);  // (F_x, F_y) at [2q]
+#pragma unroll 4
+    for (int i = 0; i < cnt; i++) {
+        const float2 F = fs[2 * (int)sl.q[i][t]];
+        const float del0 = sl.d0[i][t], del1 = sl.d1[i][t];
+        fx0 += (double)(F.x * del0);
+        fy0 += (double)(F.y * del0);
+        fx1 += (double)(F.x * del1);
+        fy1 += (double)(F.y * del1);
+    }
+}
+
 }  // namespace
 
 // The fluid-independent plan of every band tile, for every iteration slot of a kinematics batch:
@@ -380,7 +439,9 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
 // on tall grids only the band tiles are launched here and lb_fused_v2 takes the rows above.
 // p.M and p.prog point at the iteration's slot.
 __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
-    __shared__ TileMarkers sh;  // 44 KB
+    extern __shared__ __align__(16) unsigned char smem_raw[];  // kTileSmemBytes, dynamic
+    TileMarkers &sh = *reinterpret_cast<TileMarkers *>(smem_raw);
+    SpreadLists &sl = *reinterpret_cast<SpreadLists *>(smem_raw + sizeof(TileMarkers));
     const LbParams &lp = p.lb;
     const Lattice &L = lp.L;
     const int tile_y = blockIdx.x, tile_x = blockIdx.y;
@@ -431,6 +492,11 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
                 sh.wy[e] = p.M.wy[k];
             }
         }
+    }
+    int nlist = 0;
+    if (n > 0) {
+        __syncthreads();  // the staged markers
+        nlist = build_spread_list(sh, sl, n, x + L.x0, y0, hit);
     }
     pdl_wait();
     TSTAMP(1);
@@ -492,7 +558,8 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
         __syncthreads();
         TSTAMP(7);
         double fx0 = 0., fy0 = 0., fx1 = 0., fy1 = 0.;
-        tile_spread(sh, n, x + L.x0, y0, hit, fx0, fy0, fx1, fy1);
+        list_spread(sh, sl, nlist, fx0, fy0, fx1, fy1);
+        tile_spread(sh, n, x + L.x0, y0, hit, fx0, fy0, fx1, fy1);  // what did not fit the list
         Fx0 += fx0; Fy0 += fy0; Fx1 += fx1; Fy1 += fy1;
         TSTAMP(8);
     }
@@ -512,6 +579,13 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
         for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
         if (lane == 0) lp.qacc[tile_y] += s / (double)L.YDIM;
     }
+}
+
+// dynamic shared memory of lb_ib_tile_step (above the 48 KB static limit: opt-in per device)
+size_t tile_step_smem_bytes() { return sizeof(TileMarkers) + sizeof(SpreadLists); }
+cudaError_t tile_step_prepare() {
+    return cudaFuncSetAttribute(lb_ib_tile_step, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)tile_step_smem_bytes());
 }
 
 // last node of a captured batch of iterations: the iteration counter the batch reads

@@ -33,6 +33,8 @@ __global__ void ib_spread(const IbParams p);
 __global__ void ib_tile_lists(const BandParams p);
 __global__ void lb_ib_tile_step(const BandParams p);
 __global__ void it_advance(int *it_ptr, int by);
+size_t tile_step_smem_bytes();
+cudaError_t tile_step_prepare();  // once per device before the first launch
 __global__ void slab_wait(const volatile int *flag_l, const volatile int *flag_r, int need);
 __global__ void slab_signal(int *left_flag, int *right_flag, int value);
 

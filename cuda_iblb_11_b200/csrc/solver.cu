@@ -264,7 +264,8 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
             s->tiles_x = (L.W + 7) / 8;
             s->band_tiles = s->band_rows / 64;
             const size_t nt = (size_t)kKinBatch * s->band_tiles * s->tiles_x;
-            cudaError_t e = cudaMalloc((void **)&s->prog, sizeof(TileProgram) * nt);
+            cudaError_t e = tile_step_prepare();
+            if (e == cudaSuccess) e = cudaMalloc((void **)&s->prog, sizeof(TileProgram) * nt);
             if (e == cudaSuccess) e = cudaMemset(s->prog, 0, sizeof(TileProgram) * nt);
 #ifdef IBLB_TILE_TIMING
             const size_t nd = (size_t)(L.YDIM / 64) * s->tiles_x * 16;

@@ -171,6 +171,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         memset(&cfg, 0, sizeof cfg);
         cfg.gridDim = g;
         cfg.blockDim = dim3(256);
+        cfg.dynamicSmemBytes = tile_step_smem_bytes();
         cfg.stream = st;
         cudaLaunchAttribute attr;
         attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
