@@ -326,6 +326,7 @@ def test_graph_replay_equals_direct_launches():
 @pytest.mark.parametrize("c_num,c_space,c_fraction,Y", [
     (6, 48, 1, 192), (6, 48, 6, 192), (12, 48, 5, 192), (12, 48, 12, 256), (4, 64, 3, 192),
     (16, 128, 16, 192), (5, 40, 2, 192), (2, 192, 1, 128),
+    (5, 44, 5, 192),  # XDIM = 220: the last column tile hangs over the channel's edge
 ])
 def test_fused_single_launch_step_equals_separate_kernels(c_num, c_space, c_fraction, Y):
     """Interpolation and spreading fused into the LB kernel (default: lb_ib_tile_step, ONE launch
@@ -355,6 +356,28 @@ def test_fused_single_launch_step_equals_separate_kernels(c_num, c_space, c_frac
             assert s.Q == b.Q and s.it == b.it
     for s in (a, b, c, d):
         s.close()
+
+
+def test_fused_step_reports_tile_overflow_instead_of_wrong_results():
+    """A carpet far denser than any reference script (16 cilia 12 columns apart: every 8-column tile
+    sees more cilia / markers than the fused kernel's per-tile capacity): the fused path either
+    handles it bit for bit, or the next getter fails and names IBLB_FLAG_NO_FUSE — never a silent
+    difference."""
+    kw = dict(c_num=16, c_space=12, c_fraction=16)
+    b = Solver(Params.channel(192, 192, flags=FLAG_NO_FUSE | FLAG_NO_GRAPH, **kw))
+    b.step(3)
+    ref = b.fields()
+    a = Solver(Params.channel(192, 192, **kw))
+    a.step(3)
+    try:
+        got = a.fields()
+    except Exception as e:
+        assert "IBLB_FLAG_NO_FUSE" in str(e)
+    else:
+        for x, y in zip(got, ref):
+            assert np.array_equal(x, y, equal_nan=True)
+    a.close()
+    b.close()
 
 
 def test_results_are_run_to_run_deterministic():
