@@ -22,10 +22,11 @@ int cuda_fail(cudaError_t e, const char *what);
 __global__ void lb_fused_v2(const LbParams p);
 __global__ void lb_fused_v1(const LbParams p, double *qpart);
 __global__ void flux_reduce_v1(const double *qpart, int n, double *qacc);
-__global__ void lb_init(const LbParams p, const double *rho_in, const double *u_in, double u0_amp);
+__global__ void lb_init(const LbParams p, const double *rho_in, const double *u_in, double u0_amp,
+                        int row0, int nrows);
 __global__ void halo_push(const Lattice L, const double *buf, Remote left, Remote right);
-__global__ void lb_moments(const LbParams p, int streamed, double *rho_out, double *u_out,
-                           double *f_out, double *force_out);
+__global__ void lb_moments(const LbParams p, int streamed, int row0, int nrows, double *rho_out,
+                           double *u_out, double *f_out, double *force_out);
 __global__ void ib_coef(const int *k_of_j, float *coef);
 __global__ void ib_kinematics_batch(const IbParams p);
 __global__ void ib_interp(const IbParams p);
@@ -33,6 +34,8 @@ __global__ void ib_spread(const IbParams p);
 __global__ void ib_tile_lists(const BandParams p);
 __global__ void lb_ib_tile_step(const BandParams p);
 __global__ void it_advance(int *it_ptr, int by);
+constexpr size_t kStageDoubles = (size_t)16 << 20;  // 128 MB
+int stage_buffer(iblb_solver *s);  // lazily allocates s->stage_dev
 size_t tile_step_smem_bytes();
 cudaError_t tile_step_prepare();  // once per device before the first launch
 __global__ void slab_wait(const volatile int *flag_l, const volatile int *flag_r, int need);
@@ -71,6 +74,7 @@ struct iblb_solver {
     // flux
     double *qacc, *qpart;
     double *q_host;            // pinned: nq flux partial sums + the device error flag (one sync)
+    double *stage_dev;         // kStageDoubles: row chunks of fields on their way to / from the host
     int nq;
     bool flux_on;
     int xq_local;

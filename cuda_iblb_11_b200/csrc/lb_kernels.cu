@@ -138,15 +138,18 @@ __global__ void flux_reduce_v1(const double *qpart, int n, double *qacc) {
 // Initial state (main.cu:636-654, 722-754): f = f0(rho,u); stored post-collision:
 // f* = f0 + F(u, g) because TRT leaves an equilibrium unchanged.  rho/u come from device arrays
 // in the reference layout (j = y*W + x) or, when null, rho = 1, u_x = u0_amp*sin(2pi(y+.5)/Y).
-__global__ void lb_init(const LbParams p, const double *rho_in, const double *u_in, double u0_amp) {
+// Rows [row0, row0 + nrows) per launch: rho_in / u_in hold that chunk only (plane stride W*nrows),
+// so that the host never needs a device copy of the whole field.
+__global__ void lb_init(const LbParams p, const double *rho_in, const double *u_in, double u0_amp,
+                        int row0, int nrows) {
     const Lattice &L = p.L;
     const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (gid >= (long long)L.W * L.YDIM) return;
-    const int x = (int)(gid / L.YDIM), y = (int)(gid - (long long)x * L.YDIM);
+    if (gid >= (long long)L.W * nrows) return;
+    const int x = (int)(gid / nrows), y = row0 + (int)(gid - (long long)x * nrows);
     double rho = 1.0, ux, uy = 0.0;
     const double kTwoPi = 6.283185307179586476925286766559;
     if (rho_in != nullptr) {
-        const long long j = (long long)y * L.W + x, size = (long long)L.W * L.YDIM;
+        const long long j = (long long)(y - row0) * L.W + x, size = (long long)L.W * nrows;
         rho = rho_in[j];
         ux = u_in[j];
         uy = u_in[size + j];
@@ -193,14 +196,16 @@ __global__ void halo_push(const Lattice L, const double *buf, Remote left, Remot
 // Macroscopic fields / streamed populations of the last completed iteration, recomputed from the
 // buffer that iteration pulled from (still intact: the step wrote the other buffer).  Output in
 // the reference layouts.  `streamed` false = iteration 0 (no step yet): local moments.
-__global__ void lb_moments(const LbParams p, int streamed, double *rho_out, double *u_out,
-                           double *f_out, double *force_out) {
+// Rows [row0, row0 + nrows) per launch, written to chunk-local arrays (plane stride W*nrows).
+__global__ void lb_moments(const LbParams p, int streamed, int row0, int nrows, double *rho_out,
+                           double *u_out, double *f_out, double *force_out) {
     const Lattice &L = p.L;
     const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long long size = (long long)L.W * L.YDIM;
+    const long long size = (long long)L.W * nrows;
     if (gid >= size) return;
     // x fastest here so that the reference-layout stores coalesce
-    const int y = (int)(gid / L.W), x = (int)(gid - (long long)y * L.W);
+    const int yl = (int)(gid / L.W), x = (int)(gid - (long long)yl * L.W);
+    const int y = row0 + yl;
     const long long P = L.plane;
     double f[9];
 #pragma unroll

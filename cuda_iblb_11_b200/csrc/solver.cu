@@ -1,5 +1,6 @@
 // libiblb: solver lifecycle and the time-step loop (replaces main.cu:389-587, 634-754, 817-934).
 #include <cmath>
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -94,16 +95,43 @@ IbParams make_ib_params(const iblb_solver *s, int src_idx, int slot) {
     return q;
 }
 
+int stage_buffer(iblb_solver *s) {
+    if (s->stage_dev) return IBLB_OK;
+    IBLB_CUDA(cudaMalloc((void **)&s->stage_dev, sizeof(double) * kStageDoubles));
+    return IBLB_OK;
+}
+
 }  // namespace iblb
 
 using namespace iblb;
 
-static int init_state(iblb_solver *s, const double *rho_dev, const double *u_dev) {
+// rho, u: HOST arrays in the reference layout (main.cu:469-483), or null for the initial state of
+// main.cu:636-654.  Uploaded in chunks of rows through the staging buffer: no device copy of the
+// whole field (24 B/node would not fit beside the populations of the largest grids).
+static int init_state(iblb_solver *s, const double *rho, const double *u) {
     LbParams q = make_lb_params(s, 0);
     q.dst = s->buf[0];
-    const long long n = (long long)s->L.W * s->L.YDIM;
-    lb_init<<<(unsigned)((n + 255) / 256), 256, 0, s->stream>>>(q, rho_dev, u_dev, s->p.u0_amp);
-    IBLB_CUDA(cudaGetLastError());
+    const int W = s->L.W, Y = s->L.YDIM;
+    const size_t size = (size_t)W * Y;
+    if (rho == nullptr) {
+        lb_init<<<(unsigned)((size + 255) / 256), 256, 0, s->stream>>>(q, nullptr, nullptr,
+                                                                       s->p.u0_amp, 0, Y);
+        IBLB_CUDA(cudaGetLastError());
+    } else {
+        int rc = stage_buffer(s);
+        if (rc) return rc;
+        const int rows = (int)std::max<size_t>(1, std::min<size_t>(Y, kStageDoubles / (3 * (size_t)W)));
+        for (int r0 = 0; r0 < Y; r0 += rows) {
+            const int nr = std::min(rows, Y - r0);
+            const size_t cs = (size_t)W * nr, o = (size_t)W * r0;
+            double *d = s->stage_dev;
+            IBLB_CUDA(cudaMemcpyAsync(d, rho + o, sizeof(double) * cs, cudaMemcpyHostToDevice, s->stream));
+            IBLB_CUDA(cudaMemcpyAsync(d + cs, u + o, sizeof(double) * cs, cudaMemcpyHostToDevice, s->stream));
+            IBLB_CUDA(cudaMemcpyAsync(d + 2 * cs, u + size + o, sizeof(double) * cs, cudaMemcpyHostToDevice, s->stream));
+            lb_init<<<(unsigned)((cs + 255) / 256), 256, 0, s->stream>>>(q, d, d + cs, s->p.u0_amp, r0, nr);
+            IBLB_CUDA(cudaGetLastError());
+        }
+    }
     // ghost columns of buffer 0 (own opposite edge, or the connected neighbours)
     dim3 g((s->L.YDIM + 255) / 256, s->L.G, 9);
     halo_push<<<g, 256, 0, s->stream>>>(s->L, s->buf[0], s->nb[0][0], s->nb[1][0]);
@@ -350,6 +378,7 @@ int iblb_destroy(iblb_solver *s) {
     }
     cudaFree(s->buf[0]); cudaFree(s->buf[1]); cudaFree(s->qacc); cudaFree(s->qpart);
     if (s->q_host) cudaFreeHost(s->q_host);
+    cudaFree(s->stage_dev);
     cudaFree(s->flags); cudaFree(s->band); cudaFree(s->M.s); cudaFree(s->M.u_s);
     cudaFree(s->M.F_s); cudaFree(s->M.eps); cudaFree(s->M.bbox); cudaFree(s->coef);
     cudaFree(s->M.wx); cudaFree(s->M.wy); cudaFree(s->M.base);
@@ -387,20 +416,7 @@ int iblb_set_fields(iblb_solver *s, const double *rho, const double *u) {
         return IBLB_EINVAL;
     }
     IBLB_CUDA(cudaSetDevice(s->device));
-    const size_t size = (size_t)s->L.W * s->L.YDIM;
-    double *d_rho = nullptr, *d_u = nullptr;
-    IBLB_CUDA(cudaMalloc((void **)&d_rho, sizeof(double) * size));
-    cudaError_t e = cudaMalloc((void **)&d_u, sizeof(double) * 2 * size);
-    if (e != cudaSuccess) {
-        cudaFree(d_rho);
-        return cuda_fail(e, "cudaMalloc");
-    }
-    cudaMemcpyAsync(d_rho, rho, sizeof(double) * size, cudaMemcpyHostToDevice, s->stream);
-    cudaMemcpyAsync(d_u, u, sizeof(double) * 2 * size, cudaMemcpyHostToDevice, s->stream);
-    int rc = init_state(s, d_rho, d_u);
-    cudaFree(d_rho);
-    cudaFree(d_u);
-    return rc;
+    return init_state(s, rho, u);
 }
 
 }  // extern "C"

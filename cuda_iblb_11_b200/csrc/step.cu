@@ -1,5 +1,6 @@
 // libiblb: the time-step loop (replaces main.cu:817-934) and the state getters
 // (replace the D2H copies of main.cu:928, 944-982).
+#include <algorithm>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -409,32 +410,39 @@ static int run_moments(iblb_solver *s, double *rho, double *u, double *f, double
         if (rc == IBLB_OK) rc = materialise_ib(s);  // u and force need the force band
         if (rc) return rc;
     }
-    const size_t size = (size_t)s->L.W * s->L.YDIM;
-    const size_t n_out = (rho ? size : 0) + (u ? 2 * size : 0) + (f ? 9 * size : 0) +
-                         (force ? 2 * size : 0);
-    double *d = nullptr;
-    IBLB_CUDA(cudaMalloc((void **)&d, sizeof(double) * n_out));
-    double *d_rho = nullptr, *d_u = nullptr, *d_f = nullptr, *d_force = nullptr, *q = d;
-    if (rho) { d_rho = q; q += size; }
-    if (u) { d_u = q; q += 2 * size; }
-    if (f) { d_f = q; q += 9 * size; }
-    if (force) { d_force = q; q += 2 * size; }
+    // rows [r0, r0 + nr) at a time through the staging buffer: no device copy of a whole field
+    {
+        int rc = stage_buffer(s);
+        if (rc) return rc;
+    }
+    const int W = s->L.W, Y = s->L.YDIM;
+    const size_t size = (size_t)W * Y;
+    const size_t per_node = (rho ? 1 : 0) + (u ? 2 : 0) + (f ? 9 : 0) + (force ? 2 : 0);
+    const int rows = (int)std::max<size_t>(1, std::min<size_t>(Y, kStageDoubles / (per_node * W)));
     const int streamed = s->it > 0;
     LbParams lp = make_lb_params(s, streamed ? (s->cur ^ 1) : s->cur);
-    lb_moments<<<(unsigned)((size + 255) / 256), 256, 0, s->stream>>>(lp, streamed, d_rho, d_u, d_f,
-                                                                      d_force);
-    cudaError_t e = cudaGetLastError();
-    if (e == cudaSuccess && rho)
-        e = cudaMemcpyAsync(rho, d_rho, sizeof(double) * size, cudaMemcpyDeviceToHost, s->stream);
-    if (e == cudaSuccess && u)
-        e = cudaMemcpyAsync(u, d_u, sizeof(double) * 2 * size, cudaMemcpyDeviceToHost, s->stream);
-    if (e == cudaSuccess && f)
-        e = cudaMemcpyAsync(f, d_f, sizeof(double) * 9 * size, cudaMemcpyDeviceToHost, s->stream);
-    if (e == cudaSuccess && force)
-        e = cudaMemcpyAsync(force, d_force, sizeof(double) * 2 * size, cudaMemcpyDeviceToHost,
-                            s->stream);
+    cudaError_t e = cudaSuccess;
+    const cudaMemcpyKind D2H = cudaMemcpyDeviceToHost;
+    for (int r0 = 0; r0 < Y && e == cudaSuccess; r0 += rows) {
+        const int nr = std::min(rows, Y - r0);
+        const size_t cs = (size_t)W * nr, o = (size_t)W * r0, cb = sizeof(double) * cs;
+        double *d_rho = nullptr, *d_u = nullptr, *d_f = nullptr, *d_force = nullptr, *q = s->stage_dev;
+        if (rho) { d_rho = q; q += cs; }
+        if (u) { d_u = q; q += 2 * cs; }
+        if (f) { d_f = q; q += 9 * cs; }
+        if (force) { d_force = q; q += 2 * cs; }
+        lb_moments<<<(unsigned)((cs + 255) / 256), 256, 0, s->stream>>>(lp, streamed, r0, nr, d_rho,
+                                                                        d_u, d_f, d_force);
+        e = cudaGetLastError();
+        if (e == cudaSuccess && rho) e = cudaMemcpyAsync(rho + o, d_rho, cb, D2H, s->stream);
+        if (e == cudaSuccess && u) e = cudaMemcpyAsync(u + o, d_u, cb, D2H, s->stream);
+        if (e == cudaSuccess && u) e = cudaMemcpyAsync(u + size + o, d_u + cs, cb, D2H, s->stream);
+        if (e == cudaSuccess && f) e = cudaMemcpyAsync(f + 9 * o, d_f, 9 * cb, D2H, s->stream);
+        if (e == cudaSuccess && force) e = cudaMemcpyAsync(force + o, d_force, cb, D2H, s->stream);
+        if (e == cudaSuccess && force)
+            e = cudaMemcpyAsync(force + size + o, d_force + cs, cb, D2H, s->stream);
+    }
     if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
-    cudaFree(d);
     if (e != cudaSuccess) return cuda_fail(e, "iblb_get_*");
     return IBLB_OK;
 }
