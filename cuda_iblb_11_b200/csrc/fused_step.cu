@@ -564,11 +564,6 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
         TSTAMP(8);
     }
     if (!active) return;
-    // A zero force adds +-0 to every population and to the momentum: a warp none of whose nodes is
-    // forced takes the plain collision, with the same bits (populations are never exactly 0).
-    if (band_tile)
-        forced = __any_sync(0xffffffffu, (Fx0 != 0.) | (Fy0 != 0.) | (Fx1 != 0.) | (Fy1 != 0.));
-
     const double ux0 = collide_node(a, Fx0, Fy0, forced, lp);
     const double ux1 = collide_node(b, Fx1, Fy1, forced, lp);
     TSTAMP(9);

@@ -53,6 +53,7 @@ struct LbParams {
     int band_rows, band_ld;
     double omega_plus, omega_minus;  // 1/TAU, 1/TAU2 (LatticeBoltzmann.cu:80-81)
     double kforce;                   // 1 - 1/(2 TAU)  (LatticeBoltzmann.cu:56)
+    double k1I2, k1I4, k2I2, k2I4;   // kforce * w / cs^2, / cs^4 for the axis (w=1/9) and diagonal (1/36) pairs
     double gx, gy;                   // uniform body force
     double half;                     // 0.5 when the half-force velocity applies, else 0
     double *qacc;                    // per-warp running flux sums [YDIM/64] or nullptr

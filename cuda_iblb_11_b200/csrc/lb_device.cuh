@@ -34,26 +34,33 @@ __device__ __forceinline__ double2 ldg2(const double *p) {
 #define DF(a, b, c) __fma_rn((a), (b), (c))
 
 // TRT relaxation of one antiparallel pair (a = +c, b = -c) plus the Guo term.
-// LatticeBoltzmann.cu:88-134 with f0 split into its even/odd parts analytically.
+// LatticeBoltzmann.cu:88-134 with f0 split into its even/odd parts analytically.  The FP64 pipe is
+// half busy at HBM speed (the forced C2 step is 3.7 % slower than the unforced one), so the
+// operation count matters:
+//   * 0.5*(fa +- fb) - f0 is one FMA (0.5*x is exact: same bits as multiply-then-subtract);
+//   * the Guo term F_(+-c) = kw [ +-(c.F)/cs^2 - (u.F)/cs^2 + (c.u)(c.F)/cs^4 ] is split into its
+//     even part S and odd part D, which join the even / odd relaxation terms before they meet the
+//     populations: new_a = fa + (S - w+ d+) + (D - w- d-), new_b = fb + (S - w+ d+) - (D - w- d-).
+// kI4 = kw/cs^4, kI2 = kw/cs^2 per weight class; kI2uF = kI2 (u.F) per node.
 __device__ __forceinline__ void relax_pair(double &fa, double &fb, double rw, double cu,
-                                           double base, double wp, double wm, double kw,
-                                           double cF, double uF, bool forced) {
+                                           double base, double wp, double wm, bool forced,
+                                           double cF, double kI4, double kI2, double kI2uF) {
     const double f0p = DM(rw, DF(DM(cu, cu), kIcs4h, base));
     const double f0m = DM(rw, DM(cu, kIcs2));
-    const double fp = DM(0.5, DA(fa, fb));
-    const double fm = DM(0.5, DS(fa, fb));
-    const double dp = DS(fp, f0p);
-    const double dm = DS(fm, f0m);
-    double na = DF(-wm, dm, DF(-wp, dp, fa));
-    double nb = DF(wm, dm, DF(-wp, dp, fb));
+    const double dp = DF(0.5, DA(fa, fb), -f0p);
+    const double dm = DF(0.5, DS(fa, fb), -f0m);
     if (forced) {
-        const double S = DM(kw, DF(-uF, kIcs2, DM(DM(cu, cF), kIcs4)));
-        const double D = DM(kw, DM(cF, kIcs2));
-        na = DA(na, DA(S, D));
-        nb = DA(nb, DS(S, D));
+        const double A = DF(-wp, dp, DF(DM(cu, cF), kI4, -kI2uF));
+        const double B = DF(-wm, dm, DM(cF, kI2));
+        const double ta = DA(fa, A), tb = DA(fb, A);
+        fa = DA(ta, B);
+        fb = DS(tb, B);
+    } else {
+        const double na = DF(-wm, dm, DF(-wp, dp, fa));
+        const double nb = DF(wm, dm, DF(-wp, dp, fb));
+        fa = na;
+        fb = nb;
     }
-    fa = na;
-    fb = nb;
 }
 
 // moments (LatticeBoltzmann.cu:396-405, summation order i = 0..8), half-force velocity
@@ -69,14 +76,14 @@ __device__ __forceinline__ double collide_node(double (&f)[9], double Fx, double
     const double base = DF(-DF(uy, uy, DM(ux, ux)), kIcs2h, 1.0);
     const double wp = p.omega_plus, wm = p.omega_minus;
     const double uF = DF(uy, Fy, DM(ux, Fx));
-    const double k1 = DM(p.kforce, kW1), k2 = DM(p.kforce, kW2);
+    const double u1 = DM(p.k1I2, uF), u2 = DM(p.k2I2, uF);
     const double r1 = DM(rho, kW1), r2 = DM(rho, kW2);
     // rest population: no force term (LatticeBoltzmann.cu:86)
     f[0] = DF(-wp, DS(f[0], DM(DM(rho, kW0), base)), f[0]);
-    relax_pair(f[1], f[3], r1, ux, base, wp, wm, k1, Fx, uF, forced);
-    relax_pair(f[2], f[4], r1, uy, base, wp, wm, k1, Fy, uF, forced);
-    relax_pair(f[5], f[7], r2, DA(ux, uy), base, wp, wm, k2, DA(Fx, Fy), uF, forced);
-    relax_pair(f[6], f[8], r2, DS(uy, ux), base, wp, wm, k2, DS(Fy, Fx), uF, forced);
+    relax_pair(f[1], f[3], r1, ux, base, wp, wm, forced, Fx, p.k1I4, p.k1I2, u1);
+    relax_pair(f[2], f[4], r1, uy, base, wp, wm, forced, Fy, p.k1I4, p.k1I2, u1);
+    relax_pair(f[5], f[7], r2, DA(ux, uy), base, wp, wm, forced, DA(Fx, Fy), p.k2I4, p.k2I2, u2);
+    relax_pair(f[6], f[8], r2, DS(uy, ux), base, wp, wm, forced, DS(Fy, Fx), p.k2I4, p.k2I2, u2);
     return ux;
 }
 

@@ -50,6 +50,13 @@ LbParams make_lb_params(const iblb_solver *s, int src_idx) {
     q.omega_plus = 1. / s->p.TAU;
     q.omega_minus = 1. / s->p.TAU2;
     q.kforce = 1. - 1. / (2. * s->p.TAU);
+    {
+        const double cs2 = kCs * kCs, k1 = q.kforce * (1.0 / 9.0), k2 = q.kforce * (1.0 / 36.0);
+        q.k1I2 = k1 * (1.0 / cs2);
+        q.k1I4 = k1 * (1.0 / (cs2 * cs2));
+        q.k2I2 = k2 * (1.0 / cs2);
+        q.k2I4 = k2 * (1.0 / (cs2 * cs2));
+    }
     q.gx = s->p.gx;
     q.gy = s->p.gy;
     const bool half = s->p.c_num > 0 || (s->p.flags & IBLB_FLAG_HALF_FORCE_BODY);
