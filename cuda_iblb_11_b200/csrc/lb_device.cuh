@@ -42,13 +42,15 @@ __device__ __forceinline__ double2 ldg2(const double *p) {
 //     even part S and odd part D, which join the even / odd relaxation terms before they meet the
 //     populations: new_a = fa + (S - w+ d+) + (D - w- d-), new_b = fb + (S - w+ d+) - (D - w- d-).
 // kI4 = kw/cs^4, kI2 = kw/cs^2 per weight class; kI2uF = kI2 (u.F) per node.
-__device__ __forceinline__ void relax_pair(double &fa, double &fb, double rw, double cu,
-                                           double base, double wp, double wm, bool forced,
-                                           double cF, double kI4, double kI2, double kI2uF) {
+// sab = fa + fb and dab = fa - fb come from the caller, which needs them for the moments as well.
+__device__ __forceinline__ void relax_pair(double &fa, double &fb, double sab, double dab,
+                                           double rw, double cu, double base, double wp,
+                                           double wm, bool forced, double cF, double kI4,
+                                           double kI2, double kI2uF) {
     const double f0p = DM(rw, DF(DM(cu, cu), kIcs4h, base));
     const double f0m = DM(rw, DM(cu, kIcs2));
-    const double dp = DF(0.5, DA(fa, fb), -f0p);
-    const double dm = DF(0.5, DS(fa, fb), -f0m);
+    const double dp = DF(0.5, sab, -f0p);
+    const double dm = DF(0.5, dab, -f0m);
     if (forced) {
         const double A = DF(-wp, dp, DF(DM(cu, cF), kI4, -kI2uF));
         const double B = DF(-wm, dm, DM(cF, kI2));
@@ -67,9 +69,16 @@ __device__ __forceinline__ void relax_pair(double &fa, double &fb, double rw, do
 // (ImmersedBoundary.cu:249-255), then equilibrium + forcing + TRT.  Returns u_x.
 __device__ __forceinline__ double collide_node(double (&f)[9], double Fx, double Fy, bool forced,
                                                const LbParams &p) {
-    const double rho = DA(DA(DA(DA(DA(DA(DA(DA(f[0], f[1]), f[2]), f[3]), f[4]), f[5]), f[6]), f[7]), f[8]);
-    const double mx = DA(DS(DS(DA(DS(f[1], f[3]), f[5]), f[6]), f[7]), f[8]);
-    const double my = DS(DS(DA(DA(DS(f[2], f[4]), f[5]), f[6]), f[7]), f[8]);
+    // sums and differences of the four antiparallel pairs serve the moments and the relaxation
+    // (the order of LatticeBoltzmann.cu:396-405 is kept where it decides a float rounding: the
+    // interpolation's moments in ib_device.cuh / fused_step.cu; here the result feeds FP64 only)
+    const double s13 = DA(f[1], f[3]), d13 = DS(f[1], f[3]);
+    const double s24 = DA(f[2], f[4]), d24 = DS(f[2], f[4]);
+    const double s57 = DA(f[5], f[7]), d57 = DS(f[5], f[7]);
+    const double s68 = DA(f[6], f[8]), d68 = DS(f[6], f[8]);
+    const double rho = DA(DA(f[0], DA(s13, s24)), DA(s57, s68));
+    const double mx = DS(DA(d13, d57), d68);
+    const double my = DA(DA(d24, d57), d68);
     const double ir = __drcp_rn(rho);
     const double ux = DM(DF(p.half, Fx, mx), ir);
     const double uy = DM(DF(p.half, Fy, my), ir);
@@ -80,10 +89,10 @@ __device__ __forceinline__ double collide_node(double (&f)[9], double Fx, double
     const double r1 = DM(rho, kW1), r2 = DM(rho, kW2);
     // rest population: no force term (LatticeBoltzmann.cu:86)
     f[0] = DF(-wp, DS(f[0], DM(DM(rho, kW0), base)), f[0]);
-    relax_pair(f[1], f[3], r1, ux, base, wp, wm, forced, Fx, p.k1I4, p.k1I2, u1);
-    relax_pair(f[2], f[4], r1, uy, base, wp, wm, forced, Fy, p.k1I4, p.k1I2, u1);
-    relax_pair(f[5], f[7], r2, DA(ux, uy), base, wp, wm, forced, DA(Fx, Fy), p.k2I4, p.k2I2, u2);
-    relax_pair(f[6], f[8], r2, DS(uy, ux), base, wp, wm, forced, DS(Fy, Fx), p.k2I4, p.k2I2, u2);
+    relax_pair(f[1], f[3], s13, d13, r1, ux, base, wp, wm, forced, Fx, p.k1I4, p.k1I2, u1);
+    relax_pair(f[2], f[4], s24, d24, r1, uy, base, wp, wm, forced, Fy, p.k1I4, p.k1I2, u1);
+    relax_pair(f[5], f[7], s57, d57, r2, DA(ux, uy), base, wp, wm, forced, DA(Fx, Fy), p.k2I4, p.k2I2, u2);
+    relax_pair(f[6], f[8], s68, d68, r2, DS(uy, ux), base, wp, wm, forced, DS(Fy, Fx), p.k2I4, p.k2I2, u2);
     return ux;
 }
 
