@@ -327,6 +327,7 @@ def test_graph_replay_equals_direct_launches():
     (6, 48, 1, 192), (6, 48, 6, 192), (12, 48, 5, 192), (12, 48, 12, 256), (4, 64, 3, 192),
     (16, 128, 16, 192), (5, 40, 2, 192), (2, 192, 1, 128),
     (5, 44, 5, 192),  # XDIM = 220: the last column tile hangs over the channel's edge
+    (32, 128, 32, 192),  # wide: 1536 tiles, five per SM
 ])
 def test_fused_single_launch_step_equals_separate_kernels(c_num, c_space, c_fraction, Y):
     """Interpolation and spreading fused into the LB kernel (default: lb_ib_tile_step, ONE launch
