@@ -185,11 +185,11 @@ __device__ __forceinline__ void tile_marker_force(TileMarkers &sh, int tx0, int 
             const int c = c0 + cx * kTabY + cy;
             const double rho = sh.rho[c];
             const float del = dx[cx + 1] * dy[cy + 1];  // float product (ImmersedBoundary.cu:78)
-            tx[i] = ty[i] = 0.;
-            if (rho != 0.) {
-                tx[i] = interp_product(del, rho, su.z, sh.ux[c]);
-                ty[i] = interp_product(del, rho, su.w, sh.uy[c]);
-            }
+            // no branch (the nine terms overlap); a node off the array (rho = 0) contributes +0
+            const double px = interp_product(del, rho, su.z, sh.ux[c]);
+            const double py = interp_product(del, rho, su.w, sh.uy[c]);
+            tx[i] = rho != 0. ? px : 0.;
+            ty[i] = rho != 0. ? py : 0.;
         }
 #pragma unroll
         for (int i = 0; i < 9; i++) {
