@@ -511,7 +511,7 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
 
     // the support nodes in the two rings around the tile: the first 256 are pulled into registers
     // now and turned into moments after this thread's own nodes, so that their latency overlaps
-    double rf[9];
+    double rf[9] = {1., 0., 0., 0., 0., 0., 0., 0., 0.};
     bool rvalid = false;
     int rc0 = 0;
     if (t < nring) {
@@ -539,15 +539,22 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
     if (n > 0) {
         if (active) {  // this thread's support nodes: moments of the populations it pulled anyway
             const int c = (warp + 2) * kTabY + 2 * lane + 2;
-            if (own & 1) node_moments(a, sh.rho[c], sh.ux[c], sh.uy[c]);
-            if (own & 2) node_moments(b, sh.rho[c + 1], sh.ux[c + 1], sh.uy[c + 1]);
+            // a warp with any support node forms both nodes' moments in every lane, without
+            // branches (the two divisions per node overlap); cells nobody needs are never read
+            if (__any_sync(0xffffffffu, own != 0)) {
+                double r0_, x0_, y0_, r1_, x1_, y1_;
+                node_moments(a, r0_, x0_, y0_);
+                node_moments(b, r1_, x1_, y1_);
+                sh.rho[c] = r0_; sh.ux[c] = x0_; sh.uy[c] = y0_;
+                sh.rho[c + 1] = r1_; sh.ux[c + 1] = x1_; sh.uy[c + 1] = y1_;
+            }
         }
         if (t < nring) {
-            double rho = 0., ux = 0., uy = 0.;
-            if (rvalid) node_moments(rf, rho, ux, uy);
-            sh.rho[rc0] = rho;
-            sh.ux[rc0] = ux;
-            sh.uy[rc0] = uy;
+            double rho, ux, uy;
+            node_moments(rf, rho, ux, uy);  // rf = (1, 0, ...) placeholder when !rvalid
+            sh.rho[rc0] = rvalid ? rho : 0.;
+            sh.ux[rc0] = rvalid ? ux : 0.;
+            sh.uy[rc0] = rvalid ? uy : 0.;
         }
         TSTAMP(4);
         __syncthreads();
