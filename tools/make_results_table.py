@@ -24,7 +24,7 @@ txt = """
 |---|---|---|---|
 | C2 | **%.0f MLUPS**, %.3f ms/step, %.1f GB/s of algorithmic traffic = **%.1f %%** of the measured HBM copy peak (%.1f GB/s); ncu DRAM traffic %.3f GB per launch vs %.3f GB algorithmic; e2e (host buffers in and out) %.0f MLUPS | %.0f MLUPS, %.2f ms/step | `r01_bench_c2_final.json`, `r01_bench_ref_c2_final.json`; CPU oracle port on %s host threads: %s MLUPS |
 | C2 weak scaling | %.0f / %.0f / %.0f MLUPS on 2 / 4 / 8 GPUs (8192 columns per GPU) | single GPU only | `r01_bench_c2_n{2,4,8}.json` |
-| C3 | **%.0f MLUPS = %.1f us/step**, one kernel launch per iteration; e2e %.0f MLUPS | %.0f MLUPS = %.0f us/step | `r01_bench_c3_final.json`, `r01_bench_ref_c3_final.json`; IB share ~42 %% by differencing against pure LB on the same grid (target 10 %% not met, DESIGN.md section 3) |
+| C3 | **%.0f MLUPS = %.1f us/step**, one kernel launch per iteration; e2e %.0f MLUPS | %.0f MLUPS = %.0f us/step | `r01_bench_c3_final.json`, `r01_bench_ref_c3_final.json`; IB share ~39 %% by differencing against pure LB on the same grid (target 10 %% not met, DESIGN.md section 3) |
 | C1 | %.0f MLUPS = %.1f us/step | 275 us/step (`r01_diag_vs_reference_cuda.log`) | `r01_bench_c1_final.json` |
 | C4 | %.0f / %.0f / %.0f / %.0f MLUPS on 1 / 2 / 4 / 8 GPUs (strong scaling), **%.1f %%** parallel efficiency at 8 | cannot address this grid (32-bit `9*j`) | `r01_bench_c4_n{1,2,4,8}.json` |
 | C5 | %.0f MLUPS aggregate, 8 independent replicas of C1, one per GPU | runs the lines sequentially on one GPU | `r01_bench_c5_n8.json`; launcher `python -m cuda_iblb_11_b200.sweep` |
