@@ -101,8 +101,8 @@ __device__ __forceinline__ int cta_rank(bool take, int *wcount, int &total) {
     return r;
 }
 
-// moment-table cell of ring node idx in [0, kRingNodes)
-__device__ __forceinline__ int ring_cell(int idx) {
+// moment-table cell of ring node idx in [0, 4*kTabY + 4*tw) of a tile tw columns wide
+__device__ __forceinline__ int ring_cell(int idx, int tw) {
     int lx, ly;
     if (idx < 2 * kTabY) {  // two columns left of the tile
         lx = idx / kTabY;
@@ -111,11 +111,12 @@ __device__ __forceinline__ int ring_cell(int idx) {
         const int r = idx - 2 * kTabY;
         lx = r / kTabY;
         ly = r - lx * kTabY;
-        lx += 10;
+        lx += tw + 2;
     } else {  // two rows below, two above
         const int r = idx - 4 * kTabY;
-        lx = 2 + (r & 7);
-        ly = (r >> 3) < 2 ? (r >> 3) : 64 + (r >> 3);
+        const int row = r / tw;
+        lx = 2 + (r - row * tw);
+        ly = row < 2 ? row : 64 + row;
     }
     return lx * kTabY + ly;
 }
@@ -144,11 +145,12 @@ __device__ __forceinline__ void node_moments(const double (&f)[9], double &rho, 
 // table cell of the centre of a marker's 3x3 support (ImmersedBoundary.cu:108-109: nearbyint of the
 // position); false when part of the support lies outside the table — only for a marker exactly 1.5
 // off the tile, whose every weight on the tile is 0 whatever its F_s
-__device__ __forceinline__ bool marker_centre_cell(float sx, float sy, int tx0, int ty0, int &c) {
+__device__ __forceinline__ bool marker_centre_cell(float sx, float sy, int tx0, int ty0, int tw,
+                                                   int &c) {
     const int x0 = (int)nearbyint((double)sx), y0 = (int)nearbyint((double)sy);
     const int lx0 = x0 - (tx0 - 2), ly0 = y0 - (ty0 - 2);
     c = lx0 * kTabY + ly0;
-    return lx0 >= 1 && lx0 <= kTabX - 2 && ly0 >= 1 && ly0 <= kTabY - 2;
+    return lx0 >= 1 && lx0 <= tw + 2 && ly0 >= 1 && ly0 <= kTabY - 2;
 }
 
 // which of the 32 staged markers q0..q0+31 force the node pair (xg; y0, y0+1): stencil columns
@@ -166,7 +168,8 @@ __device__ __forceinline__ unsigned hit_mask32(const int2 *base, int q0, int n, 
 // F_s of staged marker e (ImmersedBoundary.cu:94-133) from the moment table: nine terms in the
 // fixed order i = 0..8, the float re-rounded after each (Q6).  The delta factors are those of the
 // spreading stencil: support column x0+c is column bx + (x0+c-bx) of it, same expression, same bits.
-__device__ __forceinline__ void tile_marker_force(TileMarkers &sh, int tx0, int ty0, int e) {
+__device__ __forceinline__ void tile_marker_force(TileMarkers &sh, int tx0, int ty0, int tw,
+                                                  int e) {
     const float4 su = sh.su[e], fb = sh.fb[e], wx = sh.wx[e], wy = sh.wy[e];
     const int x0 = (int)nearbyint((double)su.x), y0 = (int)nearbyint((double)su.y);
     const int bx = __float_as_int(fb.z), by = __float_as_int(fb.w);
@@ -175,7 +178,7 @@ __device__ __forceinline__ void tile_marker_force(TileMarkers &sh, int tx0, int 
     const float dy[3] = {oy == 1 ? wy.x : wy.y, oy == 1 ? wy.y : wy.z, oy == 1 ? wy.z : wy.w};
     float Fx = 0.f, Fy = 0.f;
     int c0;
-    if (marker_centre_cell(su.x, su.y, tx0, ty0, c0)) {
+    if (marker_centre_cell(su.x, su.y, tx0, ty0, tw, c0)) {
         // all products first (independent), then the two chains of float-rounded additions
         double tx[9], ty[9];
 #pragma unroll
@@ -350,8 +353,9 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
     const int *__restrict__ meps = p.M.eps + mo;
     const int2 *__restrict__ mbase = p.M.base + mo;
     TileProgram &pg = p.prog[((long long)slot * gridDim.x + tile_y) * p.tiles_x + tile_x];
-    const int tx0 = tile_x * 8 + L.x0, ty0 = tile_y * 64;
-    const float xlo = (float)tx0 - 1.5f, xhi = (float)(tx0 + 7) + 1.5f;
+    const int tw = p.tw;  // columns per tile = warps of lb_ib_tile_step
+    const int tx0 = tile_x * tw + L.x0, ty0 = tile_y * 64;
+    const float xlo = (float)tx0 - 1.5f, xhi = (float)(tx0 + tw - 1) + 1.5f;
     const float ylo = (float)ty0 - 1.5f, yhi = (float)(ty0 + 63) + 1.5f;
     int nrel = 0;
     for (int c0 = 0; c0 < p.c_num; c0 += 256) {
@@ -403,7 +407,7 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
         sbase[e] = mbase[k];
         const float2 sm = ms[k];
         int c0;
-        if (marker_centre_cell(sm.x, sm.y, tx0, ty0, c0)) {
+        if (marker_centre_cell(sm.x, sm.y, tx0, ty0, p.tw, c0)) {
 #pragma unroll
             for (int dx = -1; dx <= 1; dx++)
 #pragma unroll
@@ -420,9 +424,10 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
         pg.own[t] = (unsigned char)((need[c] ? 1 : 0) | (need[c + 1] ? 2 : 0));
     }
     int nring = 0;
-    for (int i0 = 0; i0 < kRingNodes; i0 += 256) {
+    const int nring_all = 4 * kTabY + 4 * tw;
+    for (int i0 = 0; i0 < nring_all; i0 += 256) {
         const int idx = i0 + t;
-        const bool take = idx < kRingNodes && need[ring_cell(idx)] != 0;
+        const bool take = idx < nring_all && need[ring_cell(idx, tw)] != 0;
         int total;
         const int r = nring + cta_rank(take, wcount, total);
         if (take) pg.ring[r] = (short)idx;
@@ -446,7 +451,8 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
     const Lattice &L = lp.L;
     const int tile_y = blockIdx.x, tile_x = blockIdx.y;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const int tx0 = tile_x * 8, ty0 = tile_y * 64;
+    const int tw = p.tw, NT = tw * 32;  // columns per tile = warps of this CTA; threads
+    const int tx0 = tile_x * tw, ty0 = tile_y * 64;
     const int x = tx0 + warp;
     const int y0 = ty0 + 2 * lane;
     const bool active = x < L.W;  // warp-uniform
@@ -472,16 +478,16 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
     if (n > 0) {  // block-uniform
         int k0 = 0, k1 = 0;
         if (t < n) k0 = __ldg(pg->list + t);
-        if (t + 256 < n) k1 = __ldg(pg->list + t + 256);
+        if (t + NT < n) k1 = __ldg(pg->list + t + NT);
         if (t < nring) r0 = __ldg(pg->ring + t);
-        if (t + 256 < nring) r1 = __ldg(pg->ring + t + 256);
+        if (t + NT < nring) r1 = __ldg(pg->ring + t + NT);
         own = __ldg(pg->own + t);
 #pragma unroll
         for (int w = 0; w < kHitWords; w++)
             if (w * 32 < n) hit[w] = __ldg(&pg->hit[w][t]);
 #pragma unroll
         for (int r = 0; r < 2; r++) {
-            const int e = t + 256 * r;
+            const int e = t + NT * r;
             if (e < n) {
                 const int k = r ? k1 : k0;
                 const float2 sm = p.M.s[k], us = p.M.u_s[k];
@@ -515,12 +521,12 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
     bool rvalid = false;
     int rc0 = 0;
     if (t < nring) {
-        rc0 = ring_cell(r0);
+        rc0 = ring_cell(r0, tw);
         const int lx = rc0 / kTabY, ly = rc0 - lx * kTabY;
         rvalid = support_node_pull(L, lp.src, tx0 + L.x0 - 2 + lx, ty0 - 2 + ly, rf);
     }
     if (n > 0) {
-        if (t + 256 < nring) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, ring_cell(r1));
+        if (t + NT < nring) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, ring_cell(r1, tw));
         if (!active) {  // columns past the channel (W % 8 != 0): as the reference would address them
             const int c = (warp + 2) * kTabY + 2 * lane + 2;
             if (own & 1) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, c);
@@ -559,8 +565,8 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
         TSTAMP(4);
         __syncthreads();
         TSTAMP(5);
-        if (t < n) tile_marker_force(sh, tx0 + L.x0, ty0, t);
-        if (t + 256 < n) tile_marker_force(sh, tx0 + L.x0, ty0, t + 256);
+        if (t < n) tile_marker_force(sh, tx0 + L.x0, ty0, tw, t);
+        if (t + NT < n) tile_marker_force(sh, tx0 + L.x0, ty0, tw, t + NT);
         TSTAMP(6);
         __syncthreads();
         TSTAMP(7);

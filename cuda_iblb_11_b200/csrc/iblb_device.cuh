@@ -93,7 +93,7 @@ struct IbParams {
 constexpr int kBandMaxRel = 128;  // cilia whose bounding box may overlap one 8-column tile
 constexpr int kTileCap = 384;     // markers (epsilon != 0) whose support can touch one 8x64 tile
 constexpr int kHitWords = 4;      // precomputed 32-marker hit-mask words per thread
-constexpr int kRingNodes = 304;   // nodes of the two rings around an 8x64 tile
+constexpr int kRingNodes = 304;   // nodes of the two rings around an 8x64 tile (the widest)
 
 // Everything about one band tile at one iteration that does not depend on the fluid (the cilia are
 // prescribed), written by ib_tile_lists for a batch of iterations, read by lb_ib_tile_step.
@@ -113,7 +113,8 @@ struct BandParams {
     MarkerArrays M;          // ib_tile_lists: slot 0; lb_ib_tile_step: the iteration's slot
     int c_num, Ns;
     int band_rows;           // rows that can receive IB force (multiple of 64)
-    int tiles_x;             // column tiles = ceil(W/8)
+    int tw;                  // columns per tile (6 or 8) = warps per CTA of lb_ib_tile_step
+    int tiles_x;             // column tiles = ceil(W/tw)
     TileProgram *prog;       // [slot][band row tile][column tile]
     int *err;                // set non-zero when a tile exceeds kBandMaxRel / kTileCap
     long long *dbg;          // development timing stamps (IBLB_TILE_TIMING builds) or nullptr

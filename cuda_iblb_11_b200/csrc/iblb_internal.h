@@ -66,6 +66,7 @@ struct iblb_solver {
     bool ib_stale;             // F_s / force band not materialised for the last step
     bool pdl_chain;            // the last kernel enqueued was lb_ib_tile_step over the whole grid
     iblb::TileProgram *prog;   // per slot and band tile: fluid-independent plan (ib_tile_lists)
+    int tile_w;                // columns per tile of lb_ib_tile_step: 8, or 6 where that fills the SMs better
     int tiles_x, band_tiles;   // column tiles, band row tiles
     long long *dbg_dev;        // development timing stamps (IBLB_TILE_TIMING builds)
     long long lists_base;      // tile lists hold iterations [lists_base, lists_base + kKinBatch); -1: none

@@ -2,6 +2,7 @@
 #include <cmath>
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -296,8 +297,31 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
         }
         s->fuse_ok = !slab && s->vec2 && !(p.flags & IBLB_FLAG_NO_FUSE);
         if (s->fuse_ok) {
-            s->tiles_x = (L.W + 7) / 8;
             s->band_tiles = s->band_rows / 64;
+            {
+                // Tile width: the step of a small grid ends with its busiest SM, so take the width
+                // (8 or 6 columns = warps per CTA) that puts the fewest nodes on one SM; ties and
+                // grids that fill the machine many times over keep 8.
+                cudaDeviceProp prop;
+                int sms = 148;
+                if (cudaGetDeviceProperties(&prop, s->device) == cudaSuccess) sms = prop.multiProcessorCount;
+                const int rows = (L.YDIM / 64 > 8) ? s->band_tiles : L.YDIM / 64;
+                long long best = -1;
+                for (int tw : {8, 6}) {
+                    const long long ctas = (long long)((L.W + tw - 1) / tw) * rows;
+                    if (tw != 8 && (long long)((L.W + 7) / 8) * rows >= 4 * sms) break;
+                    const long long load = ((ctas + sms - 1) / sms) * tw;
+                    if (best < 0 || load < best) {
+                        best = load;
+                        s->tile_w = tw;
+                    }
+                }
+                if (const char *e = getenv("IBLB_TILE_W")) {
+                    const int v = atoi(e);
+                    if (v == 6 || v == 8) s->tile_w = v;
+                }
+            }
+            s->tiles_x = (L.W + s->tile_w - 1) / s->tile_w;
             const size_t nt = (size_t)kKinBatch * s->band_tiles * s->tiles_x;
             cudaError_t e = tile_step_prepare();
             if (e == cudaSuccess) e = cudaMalloc((void **)&s->prog, sizeof(TileProgram) * nt);

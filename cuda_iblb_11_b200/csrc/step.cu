@@ -27,6 +27,7 @@ BandParams make_band_params(const iblb_solver *s, int src_idx, int slot) {
     q.c_num = (int)s->p.c_num;
     q.Ns = s->Ns;
     q.band_rows = s->band_rows;
+    q.tw = s->tile_w;
     q.tiles_x = s->tiles_x;
     q.prog = s->prog + (size_t)slot * s->band_tiles * s->tiles_x;
     q.err = s->err_dev;
@@ -171,7 +172,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         cudaLaunchConfig_t cfg;
         memset(&cfg, 0, sizeof cfg);
         cfg.gridDim = g;
-        cfg.blockDim = dim3(256);
+        cfg.blockDim = dim3(32 * s->tile_w);
         cfg.dynamicSmemBytes = tile_step_smem_bytes();
         cfg.stream = st;
         cudaLaunchAttribute attr;
