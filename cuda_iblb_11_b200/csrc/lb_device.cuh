@@ -108,6 +108,7 @@ __device__ __forceinline__ void store_remote2(const Remote &r, int col, int y0, 
 struct Pulled {
     double2 v[9];
     double e2, e5, e6, e4, e7, e8;
+    bool bot, top;  // lane 0 sits on the floor / lane 31 under the ceiling: e2 / e4 are v[4].x / v[2].y
 };
 
 __device__ __forceinline__ void load_pulled(const Lattice &L, const double *__restrict__ src, int x,
@@ -126,9 +127,13 @@ __device__ __forceinline__ void load_pulled(const Lattice &L, const double *__re
     q.v[7] = ldg2(src + 7 * P + cp);  // c = (-1,-1)
     q.v[8] = ldg2(src + 8 * P + cm);  // c = (+1,-1)
     q.e2 = q.e5 = q.e6 = q.e4 = q.e7 = q.e8 = 0.;
+    // f2(x,0) <- f4(x,0) and f4(x,Y-1) <- f2(x,Y-1) are values loaded above: they are picked in
+    // shift_pulled, NOT here — touching v[] now would stall the issue of the loads that follow
+    // (edge values, the IB ring) for a whole memory latency
+    q.bot = at_bottom;
+    q.top = at_top;
     if (lane == 0) {
         if (at_bottom) {
-            q.e2 = q.v[4].x;  // f2(x,0) <- f4(x,0): already loaded (same column, row y0)
             q.e5 = __ldg(src + 7 * P + c0);
             q.e6 = __ldg(src + 8 * P + c0);
         } else {
@@ -139,7 +144,6 @@ __device__ __forceinline__ void load_pulled(const Lattice &L, const double *__re
     }
     if (lane == 31) {
         if (at_top) {
-            q.e4 = q.v[2].y;  // f4(x,Y-1) <- f2(x,Y-1)
             q.e7 = __ldg(src + 6 * P + c0 + 1);
             q.e8 = __ldg(src + 5 * P + c0 + 1);
         } else {
@@ -157,10 +161,10 @@ __device__ __forceinline__ void shift_pulled(const Pulled &q, int lane, double (
     a[1] = q.v[1].x; b[1] = q.v[1].y;
     a[3] = q.v[3].x; b[3] = q.v[3].y;
     double t;
-    t = shfl_up1(q.v[2].y); a[2] = lane == 0 ? q.e2 : t; b[2] = q.v[2].x;
+    t = shfl_up1(q.v[2].y); a[2] = lane == 0 ? (q.bot ? q.v[4].x : q.e2) : t; b[2] = q.v[2].x;
     t = shfl_up1(q.v[5].y); a[5] = lane == 0 ? q.e5 : t; b[5] = q.v[5].x;
     t = shfl_up1(q.v[6].y); a[6] = lane == 0 ? q.e6 : t; b[6] = q.v[6].x;
-    t = shfl_dn1(q.v[4].x); a[4] = q.v[4].y; b[4] = lane == 31 ? q.e4 : t;
+    t = shfl_dn1(q.v[4].x); a[4] = q.v[4].y; b[4] = lane == 31 ? (q.top ? q.v[2].y : q.e4) : t;
     t = shfl_dn1(q.v[7].x); a[7] = q.v[7].y; b[7] = lane == 31 ? q.e7 : t;
     t = shfl_dn1(q.v[8].x); a[8] = q.v[8].y; b[8] = lane == 31 ? q.e8 : t;
 }
