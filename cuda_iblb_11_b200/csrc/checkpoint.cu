@@ -24,6 +24,8 @@
 #include <string>
 #include <vector>
 
+#include <unistd.h>
+
 #include "iblb_internal.h"
 
 using namespace iblb;
@@ -59,9 +61,12 @@ int iblb_save_checkpoint(iblb_solver *s, const char *path) {
     }
     IBLB_CUDA(cudaSetDevice(s->device));
     IBLB_CUDA(cudaStreamSynchronize(s->stream));
-    FILE *fp = fopen(path, "wb");
+    // written beside the target and renamed over it once complete and on disk: a crash or kill
+    // during the (multi-GB, seconds-long) write leaves the previous checkpoint intact
+    const std::string tmp = std::string(path) + ".tmp";
+    FILE *fp = fopen(tmp.c_str(), "wb");
     if (!fp) {
-        set_error(std::string("iblb_save_checkpoint: cannot open ") + path);
+        set_error(std::string("iblb_save_checkpoint: cannot open ") + tmp);
         return IBLB_EIO;
     }
     const uint64_t psz = sizeof(iblb_params), pb = pop_bytes(s);
@@ -84,10 +89,20 @@ int iblb_save_checkpoint(iblb_solver *s, const char *path) {
             ok = e == cudaSuccess && fwrite(stage.data(), 1, n, fp) == n;
         }
     }
+    ok = ok && fflush(fp) == 0 && fsync(fileno(fp)) == 0;
     ok = (fclose(fp) == 0) && ok;
-    if (e != cudaSuccess) return cuda_fail(e, "iblb_save_checkpoint");
+    if (e != cudaSuccess) {
+        remove(tmp.c_str());
+        return cuda_fail(e, "iblb_save_checkpoint");
+    }
     if (!ok) {
-        set_error(std::string("iblb_save_checkpoint: short write to ") + path);
+        remove(tmp.c_str());
+        set_error(std::string("iblb_save_checkpoint: short write to ") + tmp);
+        return IBLB_EIO;
+    }
+    if (rename(tmp.c_str(), path) != 0) {
+        remove(tmp.c_str());
+        set_error(std::string("iblb_save_checkpoint: cannot rename onto ") + path);
         return IBLB_EIO;
     }
     return IBLB_OK;

@@ -72,6 +72,12 @@ __global__ void __launch_bounds__(1024) ib_kinematics_batch(const IbParams p) {
         marker_state(p.coef + j * 28, reinterpret_cast<const double2 *>(trig[e]),
                      reinterpret_cast<const double2 *>(trig[e] + 12), mm, e == 0 ? it : 0,
                      p.c_space, p.c_num, p.L.XDIM, sm, v);
+        if (p.replay != nullptr && j == p.replay_j && it >= 0 && it < p.replay_steps) {
+            // the reference's racing marker exactly as a recorded run produced it (test hook)
+            const float4 r = p.replay[(long long)it * p.c_num + mm];
+            sm = make_float2(r.x, r.y);
+            v = make_float2(r.z, r.w);
+        }
         pos[e][j] = sm;
         if (e == 0) vel[j] = v;
     }

@@ -87,6 +87,10 @@ struct IbParams {
     int r_max;               // main.cu:185
     double *band;            // force band, see LbParams
     int band_rows, band_ld;
+    // test hook (iblb_set_marker_replay): marker replay_j of cilium m at iteration it takes
+    // (s_x, s_y, u_s_x, u_s_y) = replay[it*c_num + m] for it < replay_steps
+    const float4 *replay;
+    int replay_steps, replay_j;
 };
 
 // single-launch IB+LB iteration (fused_step.cu)

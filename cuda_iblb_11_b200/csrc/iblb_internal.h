@@ -71,7 +71,11 @@ struct iblb_solver {
     long long *dbg_dev;        // development timing stamps (IBLB_TILE_TIMING builds)
     long long lists_base;      // tile lists hold iterations [lists_base, lists_base + kKinBatch); -1: none
     float reach_x, reach_y;    // bounds on the marker excursion from the cilium base
+    std::vector<float> env;    // per marker of a cilium: x lo, x hi, y lo, y hi over the beat cycle
+    int tile_bound;            // upper bound on the markers that can ever touch one tile
     int *err_dev;
+    float4 *replay_dev;        // iblb_set_marker_replay (test hook) or null
+    int replay_steps, replay_j;
     // flux
     double *qacc, *qpart;
     double *q_host;            // pinned: nq flux partial sums + the device error flag (one sync)

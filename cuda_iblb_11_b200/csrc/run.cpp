@@ -188,6 +188,7 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
     const double start = now_seconds();
 
     SnapshotWriter writer;  // BigData text files are written behind the step loop
+    long long nonfinite_it = -1;  // first output iteration at which Q was not finite
 
     // iteration `it` (0-based) is complete after it+1 steps; outputs follow iterations with
     // it % INTERVAL == 0 (main.cu:938); everything in between runs without host involvement
@@ -250,6 +251,15 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
             fsB.open(flux.c_str(), ofstream::app);
             fsB << it * p.t_scale << "\t" << Q * p.x_scale << endl;  // main.cu:1002
             fsB.close();
+            // The reference's coupling is unstable for phase-lagged cilia (its own build overflows
+            // near iteration 42 on cilia6.sh:7) and it writes NaN files to the
+            // end without a word; so does this driver, but it says so.
+            if (!std::isfinite(Q) && nonfinite_it < 0) {
+                nonfinite_it = (long long)it;
+                cerr << "app: warning: the flux is non-finite at iteration " << it
+                     << " (checked every " << INTERVAL << "); the run continues as the reference's does"
+                     << endl;
+            }
         }
         if (ckpt_path && (rc = iblb_save_checkpoint(s, ckpt_path)) != IBLB_OK) break;
         if (it == INTERVAL && INTERVAL != 0) {  // main.cu:1007-1022
@@ -291,6 +301,7 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
     fsC << secs << endl;
     // additions of this implementation (after the reference's last line)
     fsC << "MLUPS: " << (runtime > 0 ? (double)size * done / runtime / 1e6 : 0.) << endl;
+    if (nonfinite_it >= 0) fsC << "Non-finite flux from output iteration: " << nonfinite_it << endl;
     fsC.close();
     iblb_destroy(s);
     if (rc) iblb::set_error(keep);

@@ -141,18 +141,4 @@ int iblb_connect_local(iblb_solver *s, iblb_solver *left, iblb_solver *right) {
     return IBLB_OK;
 }
 
-int iblb_halo_ptrs(iblb_solver *s, int face, void **send, void **recv, size_t *bytes_per_pop,
-                   size_t *pop_stride_bytes) {
-    if (!s || face < 0 || face > 1) return IBLB_EINVAL;
-    const Lattice &L = s->L;
-    double *b = s->buf[s->cur];
-    // face 0: send our first G columns, receive into the left ghosts; face 1: last G columns /
-    // right ghosts.  Column blocks of G*ld doubles are contiguous within a population plane.
-    if (send) *send = b + L.off(face == 0 ? 0 : L.W - L.G, 0);
-    if (recv) *recv = b + L.off(face == 0 ? -L.G : L.W, 0);
-    if (bytes_per_pop) *bytes_per_pop = sizeof(double) * (size_t)L.G * L.ld;
-    if (pop_stride_bytes) *pop_stride_bytes = sizeof(double) * (size_t)L.plane;
-    return IBLB_OK;
-}
-
 }  // extern "C"

@@ -100,6 +100,9 @@ IbParams make_ib_params(const iblb_solver *s, int src_idx, int slot) {
     q.band = s->band;
     q.band_rows = s->band_rows;
     q.band_ld = s->band_ld;
+    q.replay = s->replay_dev;
+    q.replay_steps = s->replay_steps;
+    q.replay_j = s->replay_j;
     return q;
 }
 
@@ -188,7 +191,13 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
     if (p.device >= 0) IBLB_CUDA(cudaSetDevice(p.device));
     iblb_solver *s = new iblb_solver();  // value-initialised: all members zero
     s->p = p;
-    IBLB_CUDA(cudaGetDevice(&s->device));
+    {
+        cudaError_t e = cudaGetDevice(&s->device);
+        if (e != cudaSuccess) {
+            delete s;
+            return cuda_fail(e, "cudaGetDevice");
+        }
+    }
     Lattice &L = s->L;
     L.XDIM = (int)p.XDIM;
     L.YDIM = (int)p.YDIM;
@@ -254,25 +263,50 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
                            cudaMemcpyHostToDevice));
             ib_coef<<<1, 128, 0, s->stream>>>(s->k_of_j_dev, s->coef);
             TRY(cudaGetLastError());
-            // rigorous bounds on the marker excursion from the cilium base, from the coefficient
-            // table (main.cu:137-145): |x| <= 111(|a_0x|/2 + sum_n sqrt(a_nx^2 + b_nx^2))
+            // envelope of every marker over the whole beat cycle, relative to its cilium's base
+            // (main.cu:137-145): sampled at kEnvSamples phases, widened by the distance a marker can
+            // move between two samples (bound on d/dphase from the coefficients) — rigorous
             std::vector<float> cf(kMarkersPerCilium * 28);
             TRY(cudaMemcpyAsync(cf.data(), s->coef, sizeof(float) * cf.size(),
                                 cudaMemcpyDeviceToHost, s->stream));
             TRY(cudaStreamSynchronize(s->stream));
+            constexpr int kEnvSamples = 2048;
+            const double two_pi = 6.283185307179586;
+            std::vector<double> cs(kEnvSamples * 12);
+            for (int k = 0; k < kEnvSamples; k++)
+                for (int n = 1; n < 7; n++) {
+                    cs[k * 12 + 2 * (n - 1)] = cos(n * two_pi * k / kEnvSamples);
+                    cs[k * 12 + 2 * (n - 1) + 1] = sin(n * two_pi * k / kEnvSamples);
+                }
+            s->env.assign(4 * kMarkersPerCilium, 0.f);
             double rx = 0., ry = 0.;
             for (int j = 0; j < kMarkersPerCilium && rc == IBLB_OK; j++) {
                 const float *c = cf.data() + j * 28;
-                double bx = 111. * fabs((double)c[0]) * 0.5, by = 111. * fabs((double)c[1]) * 0.5;
-                for (int n = 1; n < 7; n++) {
-                    bx += 111. * hypot((double)c[2 * n], (double)c[14 + 2 * n]);
-                    by += 111. * hypot((double)c[2 * n + 1], (double)c[14 + 2 * n + 1]);
+                double lo[2] = {1e30, 1e30}, hi[2] = {-1e30, -1e30}, lip[2] = {0., 0.};
+                for (int a = 0; a < 2; a++) {
+                    for (int n = 1; n < 7; n++)
+                        lip[a] += 111. * n * two_pi * hypot((double)c[2 * n + a], (double)c[14 + 2 * n + a]);
+                    for (int k = 0; k < kEnvSamples; k++) {
+                        double v = 111. * c[a] * 0.5;
+                        for (int n = 1; n < 7; n++)
+                            v += 111. * (c[2 * n + a] * cs[k * 12 + 2 * (n - 1)] +
+                                         c[14 + 2 * n + a] * cs[k * 12 + 2 * (n - 1) + 1]);
+                        lo[a] = v < lo[a] ? v : lo[a];
+                        hi[a] = v > hi[a] ? v : hi[a];
+                    }
+                    const double margin = 0.5 * lip[a] / kEnvSamples + 0.01;  // + float rounding
+                    lo[a] -= margin;
+                    hi[a] += margin;
                 }
-                rx = bx > rx ? bx : rx;
-                ry = by > ry ? by : ry;
+                s->env[4 * j + 0] = (float)lo[0];
+                s->env[4 * j + 1] = (float)hi[0];
+                s->env[4 * j + 2] = (float)(lo[1] + 1.);  // + the translation of main.cu:198
+                s->env[4 * j + 3] = (float)(hi[1] + 1.);
+                rx = std::max(rx, std::max(fabs(lo[0]), fabs(hi[0])));
+                ry = std::max(ry, hi[1] + 1.);
             }
-            s->reach_x = (float)(rx + 0.5);
-            s->reach_y = (float)(ry + 1.0 + 0.5);  // + the translation of main.cu:198
+            s->reach_x = (float)rx;
+            s->reach_y = (float)ry;
         }
     }
 #undef TRY
@@ -322,6 +356,37 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
                 }
             }
             s->tiles_x = (L.W + s->tile_w - 1) / s->tile_w;
+            // Capacity of the per-tile plans, decided here and not at run time: an upper bound on
+            // the markers / cilia that can ever be within 1.5 of a tile, from the per-marker
+            // envelopes (positions are wrapped into [0, XDIM], main.cu:193-196).  A carpet too
+            // dense for kTileCap / kBandMaxRel runs the unfused chain (same results bit for bit).
+            {
+                const int tw = s->tile_w, ntx = s->tiles_x, nty = s->band_tiles;
+                std::vector<int> cnt((size_t)ntx * nty, 0), ccnt((size_t)ntx, 0), seen((size_t)ntx, -1);
+                for (int m = 0; m < (int)p.c_num; m++) {
+                    const double base = (double)p.c_space * (m + 0.5);
+                    for (int j = 0; j < kMarkersPerCilium; j++) {
+                        const double xl = base + s->env[4 * j] - 1.5, xh = base + s->env[4 * j + 1] + 1.5;
+                        const double yl = s->env[4 * j + 2] - 1.5, yh = s->env[4 * j + 3] + 1.5;
+                        const int ty_lo = std::max(0, (int)floor(yl / 64.)), ty_hi = std::min(nty - 1, (int)floor(yh / 64.));
+                        for (int im = -1; im <= 1; im++) {  // periodic images of the envelope
+                            const double a = xl + im * (double)L.XDIM, b = xh + im * (double)L.XDIM;
+                            const int tx_lo = std::max(0, (int)floor(a / tw)), tx_hi = std::min(ntx - 1, (int)floor(b / tw));
+                            for (int tx = tx_lo; tx <= tx_hi; tx++) {
+                                for (int ty = ty_lo; ty <= ty_hi; ty++) cnt[(size_t)ty * ntx + tx]++;
+                                if (seen[tx] != m) { seen[tx] = m; ccnt[tx]++; }
+                            }
+                        }
+                    }
+                }
+                int worst = 0, worst_c = 0;
+                for (int v : cnt) worst = std::max(worst, v);
+                for (int v : ccnt) worst_c = std::max(worst_c, v);
+                s->tile_bound = worst;
+                if (worst > kTileCap || worst_c > kBandMaxRel) s->fuse_ok = false;
+            }
+        }
+        if (s->fuse_ok) {
             const size_t nt = (size_t)kKinBatch * s->band_tiles * s->tiles_x;
             cudaError_t e = tile_step_prepare();
             if (e == cudaSuccess) e = cudaMalloc((void **)&s->prog, sizeof(TileProgram) * nt);
@@ -415,6 +480,7 @@ int iblb_destroy(iblb_solver *s) {
     cudaFree(s->M.wx); cudaFree(s->M.wy); cudaFree(s->M.base);
     cudaFree(s->k_of_j_dev); cudaFree(s->it_dev);
     cudaFree(s->prog);
+    cudaFree(s->replay_dev);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->ev_boundary) cudaEventDestroy(s->ev_boundary);
@@ -439,6 +505,38 @@ int iblb_marker_fine_index(const iblb_solver *s, unsigned j) {
         return t[j];
     }
     return s->k_of_j[j];
+}
+
+// Test hook, the product-side twin of the oracle's oracle_set_marker32_replay: marker `marker_j`
+// of every cilium takes recorded values instead of computed ones.  The reference's define_filament
+// has one genuinely timing-dependent write race (marker 32, main.cu:158-172); with the
+// values a recorded run of the reference produced, the product can be compared with that run
+// directly at the stated tolerance (tests/test_gpu_parity.py).
+int iblb_set_marker_replay(iblb_solver *s, unsigned marker_j, const float *vals, unsigned n_steps) {
+    if (!s || s->p.c_num == 0 || marker_j >= (unsigned)kMarkersPerCilium) {
+        set_error("iblb_set_marker_replay: bad argument");
+        return IBLB_EINVAL;
+    }
+    IBLB_CUDA(cudaSetDevice(s->device));
+    IBLB_CUDA(cudaStreamSynchronize(s->stream));
+    cudaFree(s->replay_dev);
+    s->replay_dev = nullptr;
+    s->replay_steps = 0;
+    if (vals && n_steps > 0) {
+        const size_t nb = sizeof(float4) * (size_t)n_steps * s->p.c_num;
+        IBLB_CUDA(cudaMalloc((void **)&s->replay_dev, nb));
+        IBLB_CUDA(cudaMemcpy(s->replay_dev, vals, nb, cudaMemcpyHostToDevice));
+        s->replay_steps = (int)n_steps;
+        s->replay_j = (int)marker_j;
+    }
+    // marker slots, tile plans and captured launches hold the old kinematics
+    s->kin_base = -1;
+    s->lists_base = -1;
+    if (s->graph_exec) {
+        cudaGraphExecDestroy(s->graph_exec);
+        s->graph_exec = nullptr;
+    }
+    return IBLB_OK;
 }
 
 int iblb_set_fields(iblb_solver *s, const double *rho, const double *u) {

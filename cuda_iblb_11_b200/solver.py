@@ -96,7 +96,7 @@ SYMBOLS = [
     "iblb_get_force", "iblb_get_populations", "iblb_get_markers", "iblb_get_flux",
     "iblb_set_fields", "iblb_marker_fine_index", "iblb_last_step_seconds",
     "iblb_last_step_launches", "iblb_profile_phases", "iblb_export_halo", "iblb_connect",
-    "iblb_connect_local", "iblb_halo_ptrs", "iblb_run", "iblb_last_error", "iblb_version",
+    "iblb_connect_local", "iblb_set_marker_replay", "iblb_run", "iblb_last_error", "iblb_version",
     "iblb_save_checkpoint", "iblb_load_checkpoint",
 ]
 
@@ -139,8 +139,7 @@ def lib():
     L.iblb_export_halo.argtypes = [vp, ctypes.POINTER(HaloHandle)]
     L.iblb_connect.argtypes = [vp, ctypes.POINTER(HaloHandle), ctypes.POINTER(HaloHandle)]
     L.iblb_connect_local.argtypes = [vp, vp, vp]
-    L.iblb_halo_ptrs.argtypes = [vp, ctypes.c_int, ctypes.POINTER(vp), ctypes.POINTER(vp),
-                                 ctypes.POINTER(ctypes.c_size_t), ctypes.POINTER(ctypes.c_size_t)]
+    L.iblb_set_marker_replay.argtypes = [vp, ctypes.c_uint, vp, ctypes.c_uint]
     L.iblb_run.argtypes = [ctypes.POINTER(Params), ctypes.c_char_p]
     _lib = L
     return L
@@ -222,6 +221,16 @@ class Solver:
 
     def marker_fine_index(self, j):
         return lib().iblb_marker_fine_index(self._h, j)
+
+    def set_marker_replay(self, marker_j, vals):
+        """Test hook (iblb_set_marker_replay): vals[it, m, 0:4] = (s_x, s_y, u_s_x, u_s_y) of
+        marker `marker_j` of cilium m at iteration it, as a recorded reference run produced them."""
+        if vals is None:
+            _check(lib().iblb_set_marker_replay(self._h, marker_j, None, 0))
+            return
+        v = np.ascontiguousarray(vals, np.float32)
+        assert v.ndim == 3 and v.shape[1] == self.p.c_num and v.shape[2] == 4
+        _check(lib().iblb_set_marker_replay(self._h, marker_j, v.ctypes.data, v.shape[0]))
 
     # --- measurement ----------------------------------------------------------------------
     @property

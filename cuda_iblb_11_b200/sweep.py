@@ -94,7 +94,7 @@ def run_sweep(script_text, n_gpus=1, root="Data/", iterations=0, interval=None):
     for i, words in enumerate(runs):
         r = results.get(i)
         row = dict(run=i, gpu=None, args=" ".join(words), error="worker died", final_t=None,
-                   final_Q=None, points=0, seconds=None, mlups=None)
+                   final_Q=None, points=0, seconds=None, mlups=None, nonfinite_from_t=None)
         if r is not None:
             _, gpu, err, fname, updates, secs = r
             row.update(gpu=gpu, error=err, seconds=secs)
@@ -103,6 +103,11 @@ def run_sweep(script_text, n_gpus=1, root="Data/", iterations=0, interval=None):
                 row.update(points=len(curve), mlups=updates / secs / 1e6 if secs > 0 else None)
                 if curve:
                     row.update(final_t=curve[-1][0], final_Q=curve[-1][1])
+                    # the reference's coupling overflows on its phase-lagged lines (DESIGN.md
+                    # section 6); the run still completes, as the reference's does — say so here
+                    bad = [t for t, qv in curve if qv != qv or qv in (float("inf"), float("-inf"))]
+                    if bad:
+                        row.update(nonfinite_from_t=bad[0])
         rows.append(row)
     write_summary(rows, os.path.join(root, "Flux", "sweep-summary.tsv"))
     return rows
@@ -111,11 +116,11 @@ def run_sweep(script_text, n_gpus=1, root="Data/", iterations=0, interval=None):
 def write_summary(rows, path):
     os.makedirs(os.path.dirname(path), exist_ok=True)
     with open(path, "w") as f:
-        f.write("run\tgpu\targs\tfinal_t\tfinal_Q\tpoints\tseconds\tMLUPS\terror\n")
+        f.write("run\tgpu\targs\tfinal_t\tfinal_Q\tpoints\tseconds\tMLUPS\tnonfinite_from_t\terror\n")
         for r in rows:
             f.write("\t".join(str(r[k]) if r[k] is not None else "" for k in
                               ("run", "gpu", "args", "final_t", "final_Q", "points", "seconds",
-                               "mlups", "error")) + "\n")
+                               "mlups", "nonfinite_from_t", "error")) + "\n")
 
 
 def main(argv=None):

@@ -113,6 +113,13 @@ int iblb_get_flux(iblb_solver *s, double *Q);
 int iblb_set_fields(iblb_solver *s, const double *rho, const double *u);
 /* which fine point k in [0,9600) feeds marker j in [0,96) (main.cu:158-172) */
 int iblb_marker_fine_index(const iblb_solver *s, unsigned j);
+/* Test hook: marker `marker_j` of cilium m takes (s_x, s_y, u_s_x, u_s_y) = vals[(it*c_num + m)*4
+ * + 0..3] at iteration it < n_steps instead of the computed values (NULL / 0 switches it off).
+ * The reference's define_filament has one timing-dependent write race (marker 32, main.cu:158-172);
+ * replaying what a recorded run of the reference's CUDA build produced there lets the product be
+ * compared with that run at full tolerance.  Call before stepping. */
+int iblb_set_marker_replay(iblb_solver *s, unsigned marker_j, const float *vals,
+                           unsigned n_steps);
 
 /* ---- measurement helpers ------------------------------------------------------------------ */
 /* Device time (CUDA events on the solver's stream) of the last iblb_step call, seconds. */
@@ -142,11 +149,6 @@ int iblb_connect(iblb_solver *s, const iblb_halo_handle *left, const iblb_halo_h
  * neighbours are given as solver handles, ordering uses CUDA events instead of flags.  The caller
  * must advance all slabs in lockstep: iblb_step(slab, 1) for every slab, then the next step. */
 int iblb_connect_local(iblb_solver *s, iblb_solver *left, iblb_solver *right);
-/* Staged alternative (NCCL / host transports): device pointers of the contiguous send and
- * receive column blocks for face 0 (left) / 1 (right) of the CURRENT source buffer. */
-int iblb_halo_ptrs(iblb_solver *s, int face, void **send, void **recv, size_t *bytes_per_pop,
-                   size_t *pop_stride_bytes);
-/* In staged mode iblb_step(1) must be followed by an exchange before the next step. */
 
 /* Checkpoint / restart (new; the reference restarts its 100 000-step runs from scratch).  The file
  * holds the complete time-stepping state of this solver (both population buffers, iteration,

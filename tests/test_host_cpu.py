@@ -177,16 +177,16 @@ def test_sweep_launcher_plan_names_and_summary(tmp_path, capsys):
     f.write_text("0\t0\n0.0134\t1.25e-05\n\n0.0268\t2.5e-05\n")
     assert sweep.read_flux(str(f)) == [(0.0, 0.0), (0.0134, 1.25e-05), (0.0268, 2.5e-05)]
     rows = [dict(run=0, gpu=1, args="1 6", error=None, final_t=0.02, final_Q=1e-5, points=3,
-                 seconds=1.5, mlups=10.0),
+                 seconds=1.5, mlups=10.0, nonfinite_from_t=None),
             dict(run=1, gpu=None, args="2 6", error="worker died", final_t=None, final_Q=None,
-                 points=0, seconds=None, mlups=None)]
+                 points=0, seconds=None, mlups=None, nonfinite_from_t=0.0268)]
     out = tmp_path / "Flux" / "sweep-summary.tsv"
     sweep.write_summary(rows, str(out))
     lines = out.read_text().splitlines()
     assert lines[0].split("\t") == ["run", "gpu", "args", "final_t", "final_Q", "points", "seconds",
-                                    "MLUPS", "error"]
-    assert lines[1].split("\t") == ["0", "1", "1 6", "0.02", "1e-05", "3", "1.5", "10.0", ""]
-    assert lines[2].split("\t")[8] == "worker died"
+                                    "MLUPS", "nonfinite_from_t", "error"]
+    assert lines[1].split("\t") == ["0", "1", "1 6", "0.02", "1e-05", "3", "1.5", "10.0", "", ""]
+    assert lines[2].split("\t")[8:] == ["0.0268", "worker died"]
     script = tmp_path / "s.sh"
     script.write_text(CILIA6_SH)
     assert sweep.main([str(script), "--gpus", "8", "--dry-run"]) == 0
