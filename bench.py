@@ -151,6 +151,20 @@ class Plumbing:
         self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
         return float(t.item())
 
+    def min(self, v):
+        if not self.dist:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MIN)
+        return float(t.item())
+
+    def broadcast_object(self, obj):
+        if not self.dist:
+            return obj
+        box = [obj]
+        self.dist.broadcast_object_list(box, src=0)
+        return box[0]
+
     def all_gather_bytes(self, b):
         if not self.dist:
             return [b]
@@ -197,6 +211,156 @@ def make_solver(pl, wl, n_gpus):
     return s, p, nodes_total, Wl * w["Y"]
 
 
+def _oracle():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import checkers
+    return checkers
+
+
+def parity_c2(pl, s, p, steps_done, w):
+    """Self-check of the timed C2 run, every rank on its own columns: the forced channel is
+    x-invariant, so all columns must be EXACTLY equal, and the column profile must equal the
+    oracle's 4-column channel of the same height after the same number of steps (what
+    tests/test_gpu_slabs_fullsize.py::test_c2_full_size_equals_narrow_oracle_channel does on one
+    GPU).  The oracle is the checker here, never the thing measured."""
+    Y, W = int(p.YDIM), s.width
+    rho, u = s.fields()
+    rho = rho.reshape(Y, W)
+    ux = u[:W * Y].reshape(Y, W)
+    x_inv = bool(np.array_equal(rho, np.broadcast_to(rho[:, :1], rho.shape)) and
+                 np.array_equal(ux, np.broadcast_to(ux[:, :1], ux.shape)))
+    prof = None
+    if pl.rank == 0:
+        ck = _oracle()
+        o = ck.Checker("oracle", ck.make_params(4, Y, gx=w["gx"], threads=os.cpu_count() or 1))
+        o.step(steps_done)
+        ro, uo = o.fields()
+        o.close()
+        prof = (ro.reshape(Y, 4)[:, 0].copy(), uo[:4 * Y].reshape(Y, 4)[:, 0].copy())
+    prof = pl.broadcast_object(prof)
+    e_rho = float(np.linalg.norm(rho[:, 0] - prof[0]) / np.linalg.norm(prof[0]))
+    e_ux = float(np.linalg.norm(ux[:, 0] - prof[1]) / max(np.linalg.norm(prof[1]), 1e-300))
+    ok = x_inv and e_rho <= 1e-10 and e_ux <= 1e-10
+    ok_all = pl.min(1.0 if ok else 0.0) == 1.0
+    return {"ok": ok_all, "what": "every rank: exact x-invariance of its columns + column profile vs "
+                                  "the oracle's 4x%d channel after %d steps (tol 1e-10)" % (Y, steps_done),
+            "x_invariant": bool(pl.min(1.0 if x_inv else 0.0) == 1.0),
+            "rel_l2_rho": pl.max(e_rho), "rel_l2_ux": pl.max(e_ux)}
+
+
+C4S = dict(X=4096, Y=1024, c_num=32, c_space=128, steps=40)  # down-scaled C4 for the self-check
+
+
+def parity_c4s(pl, n):
+    """Down-scaled C4 (4096x1024, 32 cilia 128 apart): every rank steps its x-slab of the ring
+    (CUDA IPC peer stores + device flags, the bench's N>1 path) AND the whole channel on its own
+    GPU (single-launch IB+LB path, split for tall grids) and compares its columns bit for bit;
+    rank 0 also holds the whole channel against the oracle.  N = 1: fused vs unfused chain."""
+    from cuda_iblb_11_b200 import FLAG_NO_FUSE, FLAG_NO_GRAPH, HaloHandle, Params, Solver
+    c = C4S
+    X, Y, steps = c["X"], c["Y"], c["steps"]
+    kw = dict(c_num=c["c_num"], c_space=c["c_space"], c_fraction=c["c_num"], device=pl.local)
+    whole = Solver(Params.channel(X, Y, **kw))
+    whole.step(steps)
+    r2, u2 = whole.fields()
+    if n > 1:
+        Wl = X // n
+        x0 = pl.rank * Wl
+        part = Solver(Params.channel(X, Y, slab_x0=x0, slab_w=Wl, **kw))
+        mine = bytes(part.export_halo())
+        hs = [HaloHandle.from_buffer_copy(b) for b in pl.all_gather_bytes(mine)]
+        part.connect(hs[(pl.rank - 1) % n], hs[(pl.rank + 1) % n])
+        pl.barrier()
+        part.step(steps)
+        part.sync()
+        pl.barrier()
+        how = "x-slabs x%d (IPC) == whole channel, bitwise" % n
+    else:
+        Wl, x0 = X, 0
+        part = Solver(Params.channel(X, Y, flags=FLAG_NO_FUSE | FLAG_NO_GRAPH, **kw))
+        part.step(steps)
+        how = "single-launch IB+LB path == unfused kernel chain, bitwise"
+    r1, u1 = part.fields()
+    sl = slice(x0, x0 + Wl)
+    same = bool(np.array_equal(r1.reshape(Y, Wl), r2.reshape(Y, X)[:, sl]) and
+                np.array_equal(u1[:Wl * Y].reshape(Y, Wl), u2[:X * Y].reshape(Y, X)[:, sl]) and
+                np.array_equal(u1[Wl * Y:].reshape(Y, Wl), u2[X * Y:].reshape(Y, X)[:, sl]))
+    q_part = pl.sum(part.Q) if n > 1 else part.Q
+    same_q = bool(q_part == whole.Q)
+    pl.barrier()
+    part.close()
+    out = {"grid": [X, Y], "cilia": c["c_num"], "steps": steps, "how": how,
+           "bitwise_equal": bool(pl.min(1.0 if same else 0.0) == 1.0), "flux_equal": same_q}
+    if pl.rank == 0:
+        ck = _oracle()
+        o = ck.Checker("oracle", ck.make_params(X, Y, c_num=c["c_num"], c_space=c["c_space"],
+                                               c_fraction=c["c_num"], flags=ck.REF_FLAG_PICK_LOWEST_K,
+                                               threads=os.cpu_count() or 1))
+        o.step(steps)
+        ro, uo = o.fields()
+        m1, m2 = whole.markers(), o.markers()
+        out["vs_oracle"] = {"rel_l2_rho": ck.rel_l2(r2, ro), "rel_l2_u": ck.rel_l2(u2, uo),
+                            "markers_bit_equal": bool(np.array_equal(m1[0], m2[0]) and
+                                                      np.array_equal(m1[1], m2[1]) and
+                                                      np.array_equal(m1[3], m2[3])),
+                            "tol": "rho 1e-10, u 1e-8, markers bit-equal"}
+        v = out["vs_oracle"]
+        out["oracle_ok"] = bool(v["rel_l2_rho"] <= 1e-10 and v["rel_l2_u"] <= 1e-8 and
+                                v["markers_bit_equal"])
+        o.close()
+    whole.close()
+    ok = out["bitwise_equal"] and out["flux_equal"] and out.get("oracle_ok", True)
+    out["ok"] = bool(pl.min(1.0 if ok else 0.0) == 1.0)
+    return out
+
+
+def c4_leg(pl, n, steps=20, warmup=3):
+    """configs[3]: 32768x32768 + 256 cilia, x-slabs over the N GPUs (strong scaling; one GPU holds
+    all of it: 154.6 GB).  Same timing rules as the headline (device events, max over ranks)."""
+    s, p, nodes_total, nodes_local = make_solver(pl, "c4", n)
+    s.step(warmup)
+    s.sync()
+    pl.barrier()
+    s.step(steps)
+    s.sync()
+    t = pl.max(s.last_step_seconds)
+    launches = int(pl.sum(float(s.last_step_launches)))
+    q = pl.sum(s.Q) if n > 1 else s.Q
+    pl.barrier()
+    s.close()
+    return {"workload": WORKLOADS["c4"]["desc"], "grid": [int(p.XDIM), int(p.YDIM)], "n_gpus": n,
+            "scaling": "strong", "value": round(nodes_total * steps / t / 1e6, 1), "unit": "MLUPS",
+            "ms_per_step": round(1e3 * t / steps, 4), "steps": steps, "warmup": warmup,
+            "gpu_launches": launches, "flux_finite": bool(np.isfinite(q)),
+            "frac_of_measured_hbm_peak": round(BYTES_PER_LUP * nodes_total / n * steps / t / 1e9 /
+                                               measured_peak()[0], 4)}
+
+
+def ib_share_leg(device, steps=4000):
+    """IB share of the step at 12 cilia (north_star target <= 10 %): the cilia12.sh grid with its
+    cilia (single-launch IB+LB step) against the same grid as pure LB, both CUDA-graph replayed,
+    device time by events; share = (fused - pure) / fused."""
+    from cuda_iblb_11_b200 import Params, Solver
+    w = WORKLOADS["c3"]
+    res = {}
+    for name, kw in (("fused", dict(c_num=w["c_num"], c_space=w["c_space"], c_fraction=w["c_fraction"])),
+                     ("pure", dict(gx=1e-7))):
+        s = Solver(Params.channel(w["X"], w["Y"], device=device, **kw))
+        s.step(200)
+        s.sync()
+        best = 1e9
+        for _ in range(3):
+            s.step(steps)
+            s.sync()
+            best = min(best, s.last_step_seconds / steps)
+        s.close()
+        res[name] = best * 1e6
+    return {"workload": "c3: " + w["desc"], "fused_us": round(res["fused"], 3),
+            "pure_lb_us": round(res["pure"], 3), "steps": steps,
+            "share": round((res["fused"] - res["pure"]) / res["fused"], 4),
+            "how": "iblb_last_step_seconds of %d graph-replayed steps, best of 3, on two solvers" % steps}
+
+
 def run_ours(a):
     pl = Plumbing(a.gpus)
     n = max(1, a.gpus)
@@ -224,6 +388,16 @@ def run_ours(a):
     t = pl.max(t_dev)
     launches_total = int(pl.sum(float(launches)))
     value = nodes_total * a.steps / t / 1e6
+
+    # ---- self-check of the state the timed steps produced (before the e2e leg resets it) ----
+    w_cfg = WORKLOADS[a.workload]
+    parity = None
+    if not a.no_parity:
+        try:
+            if a.workload == "c2":
+                parity = {"c2": parity_c2(pl, s, p, a.warmup + a.steps, w_cfg)}
+        except Exception as e:  # reported, never hidden
+            parity = {"c2": {"ok": False, "error": "%s: %s" % (type(e).__name__, e)}}
 
     # ---- e2e: same metric through the C ABI with HOST buffers: upload (rho,u), K steps with the
     # reference's per-step flux readback (main.cu:928), download (rho,u) (main.cu:944-952) ----
@@ -269,7 +443,8 @@ def run_ours(a):
             "algorithmic_bytes_per_launch": BYTES_PER_LUP * nodes_local,
             "avg_launch_ms": round(1e3 * t_dev / a.steps, 4),
             "launches_of_kernel": lb_launches_per_rank,
-            "traffic": tr.get("dram_bytes_per_launch") if (tr and a.workload == "c2") else None}
+            # ncu capture of this kernel on one GPU over the whole channel; not measured on slabs
+            "traffic": tr.get("dram_bytes_per_launch") if (tr and a.workload == "c2" and n == 1) else None}
     out = None
     if pl.rank == 0:
         out = {
@@ -292,6 +467,28 @@ def run_ours(a):
             "roofline": roof, "clocks": clocks, "flux_check": q,
         }
     s.close()
+    # ---- further legs on the same box, reported inside the same JSON line ----
+    extras = {}
+    if not a.no_parity:
+        try:
+            c4s = parity_c4s(pl, n)
+        except Exception as e:
+            c4s = {"ok": False, "error": "%s: %s" % (type(e).__name__, e)}
+        parity = dict(parity or {}, c4s=c4s)
+        parity["ok"] = all(v.get("ok", False) for v in parity.values() if isinstance(v, dict))
+    if a.workload == "c2" and not a.no_extras:
+        try:
+            extras["c4"] = c4_leg(pl, n)
+        except Exception as e:
+            extras["c4"] = {"error": "%s: %s" % (type(e).__name__, e), "n_gpus": n}
+        if n == 1:
+            try:
+                extras["ib_share"] = ib_share_leg(pl.local)
+            except Exception as e:
+                extras["ib_share"] = {"error": "%s: %s" % (type(e).__name__, e)}
+    if out is not None:
+        out["parity"] = parity
+        out.update(extras)
     return pl, out
 
 
@@ -387,6 +584,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--force-e2e", action="store_true", help="run the host-buffer leg at any size")
+    ap.add_argument("--no-parity", action="store_true", help="skip the self-check legs")
+    ap.add_argument("--no-extras", action="store_true", help="skip the C4 and IB-share legs")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3)
     if a.impl == "reference":

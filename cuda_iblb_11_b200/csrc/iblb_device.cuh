@@ -22,6 +22,7 @@ constexpr int kMarkersPerCilium = 96;   // main.cu:83
 constexpr int kFinePoints = 9600;       // main.cu:81
 constexpr int kSpreadTileX = 8, kSpreadTileY = 32;
 constexpr int kKinBatch = 32;      // iterations of marker kinematics computed per launch
+constexpr int kSlabFlags = 4;  // slab step counters: [0],[1] data ready from the left / right neighbour; [2],[3] their release
 constexpr int kMaxLeftCilia = 16;  // r_max = 2*96/c_space (main.cu:185) must not exceed this
 
 struct Lattice {

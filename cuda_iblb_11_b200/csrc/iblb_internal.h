@@ -38,7 +38,8 @@ constexpr size_t kStageDoubles = (size_t)16 << 20;  // 128 MB
 int stage_buffer(iblb_solver *s);  // lazily allocates s->stage_dev
 size_t tile_step_smem_bytes();
 cudaError_t tile_step_prepare();  // once per device before the first launch
-__global__ void slab_wait(const volatile int *flag_l, const volatile int *flag_r, int need);
+__global__ void slab_wait(const volatile int *flags, int *rel_left, int *rel_right, int need,
+                          long long timeout_ns, int *err);
 __global__ void slab_signal(int *left_flag, int *right_flag, int value);
 
 }  // namespace iblb
@@ -94,8 +95,13 @@ struct iblb_solver {
     bool connected;
     iblb::Remote nb[2][2];     // [face 0=left,1=right][buffer parity]
     void *nb_mapped[2][2];
-    int *flags;                // [0]: written by the left neighbour, [1]: by the right one
-    int *nb_flag[2];           // left neighbour's flags[1], right neighbour's flags[0]
+    int *flags;                // kSlabFlags step counters written by the neighbours (see slab_wait)
+    int *nb_flag[2];           // left neighbour's flags[1], right neighbour's flags[0] (data ready)
+    int *nb_rel[2];            // left neighbour's flags[3], right neighbour's flags[2] (release)
+    cudaStream_t stream_b;     // coupled slabs: wait -> boundary columns -> signal run here,
+    cudaEvent_t ev_b, ev_i, ev_ib;  // beside the interior kernel on `stream` (events order them)
+    bool two_stream_primed;    // ev_b / ev_i have been recorded at least once
+    long long slab_timeout_ns; // bound on slab_wait's spin (IBLB_SLAB_TIMEOUT_S, default 60 s)
     void *nb_flag_mapped[2];
     bool self_left, self_right;
     int flag_base;             // step flags carry flag_base + it (monotonic across set_fields)

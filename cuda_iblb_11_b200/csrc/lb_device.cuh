@@ -178,15 +178,23 @@ __device__ __forceinline__ void store_pair(const LbParams &p, int x, int y0, con
 #pragma unroll
     for (int i = 0; i < 9; i++)
         *reinterpret_cast<double2 *>(dst + i * L.plane + c0) = make_double2(a[i], b[i]);
+    // Ghost columns: with one ghost column per side (pure LB) only the three populations that
+    // stream across the face are ever pulled from it — c_x = -1 (3, 6, 7) into the left
+    // neighbour's right ghost, c_x = +1 (1, 5, 8) into the right neighbour's left ghost; with
+    // cilia (G = 3) the neighbour's interpolation forms moments of ghost nodes and needs all nine.
     if (x < p.left.G) {
+        const bool all = p.left.G > 1;
 #pragma unroll
         for (int i = 0; i < 9; i++)
-            store_remote2(p.left, p.left.W + x, y0, i, make_double2(a[i], b[i]));
+            if (all || i == 3 || i == 6 || i == 7)
+                store_remote2(p.left, p.left.W + x, y0, i, make_double2(a[i], b[i]));
     }
     if (x >= L.W - p.right.G) {
+        const bool all = p.right.G > 1;
 #pragma unroll
         for (int i = 0; i < 9; i++)
-            store_remote2(p.right, x - L.W, y0, i, make_double2(a[i], b[i]));
+            if (all || i == 1 || i == 5 || i == 8)
+                store_remote2(p.right, x - L.W, y0, i, make_double2(a[i], b[i]));
     }
 }
 

@@ -103,17 +103,19 @@ __global__ void __launch_bounds__(256) lb_fused_v1(const LbParams p, double *qpa
         const long long c0 = L.off(x, y);
 #pragma unroll
         for (int i = 0; i < 9; i++) p.dst[i * P + c0] = f[i];
-        if (x < p.left.G) {
+        if (x < p.left.G) {  // see store_pair: three crossing populations when G == 1
 #pragma unroll
             for (int i = 0; i < 9; i++)
-                p.left.base[(long long)i * p.left.plane +
-                            (long long)(p.left.W + x + p.left.G) * p.left.ld + y] = f[i];
+                if (p.left.G > 1 || i == 3 || i == 6 || i == 7)
+                    p.left.base[(long long)i * p.left.plane +
+                                (long long)(p.left.W + x + p.left.G) * p.left.ld + y] = f[i];
         }
         if (x >= L.W - p.right.G) {
 #pragma unroll
             for (int i = 0; i < 9; i++)
-                p.right.base[(long long)i * p.right.plane +
-                             (long long)(x - L.W + p.right.G) * p.right.ld + y] = f[i];
+                if (p.right.G > 1 || i == 1 || i == 5 || i == 8)
+                    p.right.base[(long long)i * p.right.plane +
+                                 (long long)(x - L.W + p.right.G) * p.right.ld + y] = f[i];
         }
     }
     // flux: per-node values of the flux column go to a scratch column, reduced by flux_reduce_v1
@@ -286,14 +288,37 @@ __global__ void lb_moments(const LbParams p, int streamed, int row0, int nrows, 
 namespace iblb {
 
 // ---- slab ordering across GPUs (one process per GPU): step counters in peer-mapped memory.
-// The waiting side spins on ITS OWN memory; the writer is a kernel on another GPU, so both are
-// always resident (never used between ranks that share a GPU).
-__global__ void slab_wait(const volatile int *flag_l, const volatile int *flag_r, int need) {
-    if (threadIdx.x == 0) {
-        while (*flag_l < need) __nanosleep(100);
-        while (*flag_r < need) __nanosleep(100);
-        __threadfence_system();
+// flags[0], flags[1]: "data ready" — the left / right neighbour has stored the boundary columns of
+//   its previous iteration into this slab's ghost columns (written by its slab_signal);
+// flags[2], flags[3]: "release" — that neighbour has BEGUN this iteration, so nothing of it (no
+//   getter, no checkpoint) still reads the ghost columns of the buffer this slab's boundary kernel
+//   is about to overwrite over there.  Without it a rank that has stopped to read its fields races
+//   with a neighbour that is one step ahead (the getters pull from the previous source buffer).
+// A slab first publishes its own release, then spins on ITS OWN memory; the writers are kernels on
+// other GPUs, so both sides are always resident (never used between ranks that share a GPU).
+// The spin is bounded: when a neighbour never arrives (a rank died, or the ranks were asked for
+// different step counts) the kernel raises *err = 3 and falls through instead of hanging the GPU;
+// every later wait returns at once and the next getter / iblb_sync reports it.
+__global__ void slab_wait(const volatile int *flags, int *rel_left, int *rel_right, int need,
+                          long long timeout_ns, int *err) {
+    if (threadIdx.x != 0) return;
+    *reinterpret_cast<volatile int *>(rel_left) = need;
+    *reinterpret_cast<volatile int *>(rel_right) = need;
+    __threadfence_system();
+    if (*reinterpret_cast<volatile int *>(err) == 3) return;
+    unsigned long long t0, t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (int i = 0; i < kSlabFlags; i++) {
+        while (flags[i] < need) {
+            __nanosleep(100);
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if ((long long)(t - t0) > timeout_ns) {
+                atomicExch(err, 3);
+                return;
+            }
+        }
     }
+    __threadfence_system();
 }
 
 __global__ void slab_signal(int *left_flag, int *right_flag, int value) {

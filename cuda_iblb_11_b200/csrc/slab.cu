@@ -48,6 +48,13 @@ static int map_neighbour(iblb_solver *s, int face, const iblb_halo_handle *h) {
         if (cudaIpcGetMemHandle(&own, s->buf[0]) == cudaSuccess)
             is_own = memcmp(&own, h->mem[0], sizeof own) == 0;
     }
+    if (!is_own && h->device == s->device && h->pid != (int)getpid()) {
+        // slab_wait spins until the neighbour's kernel has run: two processes time-slicing one GPU
+        // can starve each other for ever
+        set_error("iblb_connect: the neighbour is another process on the same GPU "
+                  "(one slab per GPU; use iblb_connect_local within one process)");
+        return IBLB_EINVAL;
+    }
     if ((int)h->ghost != s->L.G || (int)h->ld != s->L.ld) {
         set_error("iblb_connect: neighbour has a different ghost width or column pitch");
         return IBLB_EINVAL;
@@ -77,8 +84,9 @@ static int map_neighbour(iblb_solver *s, int face, const iblb_halo_handle *h) {
         s->nb_flag_mapped[face] = ptr;
         flags = (int *)ptr;
     }
-    // I am the RIGHT neighbour of my left neighbour: I write its flags[1]; and vice versa
+    // I am the RIGHT neighbour of my left neighbour: I write its flags[1] / [3]; and vice versa
     s->nb_flag[face] = &flags[face == 0 ? 1 : 0];
+    s->nb_rel[face] = &flags[face == 0 ? 3 : 2];
     if (face == 0) s->self_left = is_own;
     else s->self_right = is_own;
     return IBLB_OK;
@@ -93,6 +101,16 @@ int iblb_connect(iblb_solver *s, const iblb_halo_handle *left, const iblb_halo_h
     rc = map_neighbour(s, 1, right);
     if (rc) return rc;
     s->connected = true;
+    if (!s->stream_b) {
+        // the boundary stream outranks the interior one: its small kernels must not queue behind
+        // the interior kernel's thread blocks
+        int lo = 0, hi = 0;
+        IBLB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        IBLB_CUDA(cudaStreamCreateWithPriority(&s->stream_b, cudaStreamNonBlocking, hi));
+        IBLB_CUDA(cudaEventCreateWithFlags(&s->ev_b, cudaEventDisableTiming));
+        IBLB_CUDA(cudaEventCreateWithFlags(&s->ev_i, cudaEventDisableTiming));
+        IBLB_CUDA(cudaEventCreateWithFlags(&s->ev_ib, cudaEventDisableTiming));
+    }
     if (s->graph_exec) {
         cudaGraphExecDestroy(s->graph_exec);
         s->graph_exec = nullptr;

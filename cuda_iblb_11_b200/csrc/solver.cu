@@ -229,8 +229,16 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
     TRY(cudaMalloc((void **)&s->qacc, sizeof(double) * s->nq));
     TRY(cudaMallocHost((void **)&s->q_host, sizeof(double) * (s->nq + 1)));
     if (!s->vec2) TRY(cudaMalloc((void **)&s->qpart, sizeof(double) * p.YDIM));
-    TRY(cudaMalloc((void **)&s->flags, 2 * sizeof(int)));
-    if (rc == IBLB_OK) TRY(cudaMemset(s->flags, 0, 2 * sizeof(int)));
+    TRY(cudaMalloc((void **)&s->flags, kSlabFlags * sizeof(int)));
+    if (rc == IBLB_OK) TRY(cudaMemset(s->flags, 0, kSlabFlags * sizeof(int)));
+    TRY(cudaMalloc((void **)&s->err_dev, sizeof(int)));
+    if (rc == IBLB_OK) TRY(cudaMemset(s->err_dev, 0, sizeof(int)));
+    TRY(cudaMalloc((void **)&s->it_dev, sizeof(int)));
+    {
+        const char *e = getenv("IBLB_SLAB_TIMEOUT_S");
+        const double sec = e ? atof(e) : 60.;
+        s->slab_timeout_ns = (long long)((sec > 0. ? sec : 60.) * 1e9);
+    }
     TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     TRY(cudaEventCreate(&s->ev0));
     TRY(cudaEventCreate(&s->ev1));
@@ -250,9 +258,6 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
         TRY(cudaMalloc((void **)&s->M.base, sizeof(int2) * nm));
         TRY(cudaMalloc((void **)&s->coef, sizeof(float) * kMarkersPerCilium * 28));
         TRY(cudaMalloc((void **)&s->k_of_j_dev, sizeof(int) * kMarkersPerCilium));
-        TRY(cudaMalloc((void **)&s->it_dev, sizeof(int)));
-        TRY(cudaMalloc((void **)&s->err_dev, sizeof(int)));
-        if (rc == IBLB_OK) TRY(cudaMemset(s->err_dev, 0, sizeof(int)));
         if (rc == IBLB_OK) {
             TRY(cudaMemset(s->M.s, 0, sizeof(float2) * nm));
             TRY(cudaMemset(s->M.u_s, 0, sizeof(float2) * nm));
@@ -411,6 +416,8 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
     s->self_left = s->self_right = true;
     s->nb_flag[0] = &s->flags[1];
     s->nb_flag[1] = &s->flags[0];
+    s->nb_rel[0] = &s->flags[3];
+    s->nb_rel[1] = &s->flags[2];
     rc = init_state(s, nullptr, nullptr);
     if (rc != IBLB_OK) {
         std::string keep = iblb_last_error();
@@ -484,6 +491,10 @@ int iblb_destroy(iblb_solver *s) {
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->ev_boundary) cudaEventDestroy(s->ev_boundary);
+    if (s->ev_b) cudaEventDestroy(s->ev_b);
+    if (s->ev_i) cudaEventDestroy(s->ev_i);
+    if (s->ev_ib) cudaEventDestroy(s->ev_ib);
+    if (s->stream_b) cudaStreamDestroy(s->stream_b);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
     return IBLB_OK;
@@ -491,7 +502,16 @@ int iblb_destroy(iblb_solver *s) {
 
 int iblb_sync(iblb_solver *s) {
     if (!s) return IBLB_EINVAL;
+    IBLB_CUDA(cudaSetDevice(s->device));
     IBLB_CUDA(cudaStreamSynchronize(s->stream));
+    if (s->connected && s->err_dev) {  // a slab whose neighbour never arrived says so here
+        int flag = 0;
+        IBLB_CUDA(cudaMemcpy(&flag, s->err_dev, sizeof(int), cudaMemcpyDeviceToHost));
+        if (flag == 3) {
+            set_error("slab_wait timed out: a neighbouring slab never reached this iteration");
+            return IBLB_ECUDA;
+        }
+    }
     return IBLB_OK;
 }
 

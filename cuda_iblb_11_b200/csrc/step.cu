@@ -87,14 +87,24 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
     const int src = s->cur;
     const bool coupled = s->connected && !(s->self_left && s->self_right);
     const bool local = coupled && s->peer[0] != nullptr;
+    // Slabs coupled across processes run two streams: `sb` carries what the neighbours wait for
+    // (flag wait -> marker kernels -> boundary columns -> signal), `st` the interior columns, which
+    // read no ghost column and need not sit behind the wait.  Events order the two: the boundary
+    // kernel needs the previous iteration's interior (column G-1 pulls from column G; the band),
+    // the interior needs the previous iteration's boundary kernel and this iteration's spreading.
+    const bool two = coupled && !local && !pe && !graph_mode && s->stream_b != nullptr;
+    cudaStream_t sb = two ? s->stream_b : st;
+    if (two) IBLB_CUDA(cudaStreamWaitEvent(st, s->ev_b, 0));  // boundary kernel of the PREVIOUS iteration
     if (local) {
         // same-process neighbours: their boundary kernels of the previous step (host lockstep)
         for (int f = 0; f < 2; f++)
             if (s->peer[f] != s && s->peer[f]->ev_boundary)
                 IBLB_CUDA(cudaStreamWaitEvent(st, s->peer[f]->ev_boundary, 0));
     } else if (coupled) {
-        slab_wait<<<1, 32, 0, st>>>(&s->flags[0], &s->flags[1], s->flag_base + (int)s->it);
+        slab_wait<<<1, 32, 0, sb>>>(s->flags, s->nb_rel[0], s->nb_rel[1],
+                                    s->flag_base + (int)s->it, s->slab_timeout_ns, s->err_dev);
         launches += 1;
+        if (two) IBLB_CUDA(cudaStreamWaitEvent(sb, s->ev_i, 0));  // interior of the previous iteration
     }
     if (pe) cudaEventRecord(pe->e[0], st);
     const bool fused = !pe && fused_path(s);
@@ -120,7 +130,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
                 kp.it_ptr = s->it_dev;
                 kp.it = 0;
             }
-            ib_kinematics_batch<<<dim3(kp.c_num, kKinBatch), 1024, 0, st>>>(kp);
+            ib_kinematics_batch<<<dim3(kp.c_num, kKinBatch), 1024, 0, sb>>>(kp);
             fresh_plan = true;
             launches += 1;
             IBLB_CUDA(cudaGetLastError());
@@ -140,17 +150,21 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         if (pe) cudaEventRecord(pe->e[1], st);
         IbParams ib = make_ib_params(s, src, slot);
         if (!fused) {
-            ib_interp<<<(ib.Ns + 23) / 24, 256, 0, st>>>(ib);
+            ib_interp<<<(ib.Ns + 23) / 24, 256, 0, sb>>>(ib);
             launches += 1;
             IBLB_CUDA(cudaGetLastError());
         }
         if (pe) cudaEventRecord(pe->e[2], st);
         if (!fused) {
             dim3 g((s->L.W + kSpreadTileX - 1) / kSpreadTileX, s->band_rows / kSpreadTileY);
-            ib_spread<<<g, 256, 0, st>>>(ib);
+            ib_spread<<<g, 256, 0, sb>>>(ib);
             launches += 1;
             IBLB_CUDA(cudaGetLastError());
             s->ib_stale = false;
+            if (two) {  // the interior kernel reads the force band
+                IBLB_CUDA(cudaEventRecord(s->ev_ib, sb));
+                IBLB_CUDA(cudaStreamWaitEvent(st, s->ev_ib, 0));
+            }
         }
     } else if (pe) {
         cudaEventRecord(pe->e[1], st);
@@ -198,14 +212,15 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         qb.col_count = 2 * G;
         qb.split_at = G;
         qb.split_skip = W - 2 * G;
-        int rc = launch_lb(s, qb, st, launches);
+        int rc = launch_lb(s, qb, sb, launches);
         if (rc) return rc;
         if (local) {
             IBLB_CUDA(cudaEventRecord(s->ev_boundary, st));
         } else {
-            slab_signal<<<1, 32, 0, st>>>(s->nb_flag[0], s->nb_flag[1],
+            slab_signal<<<1, 32, 0, sb>>>(s->nb_flag[0], s->nb_flag[1],
                                         s->flag_base + (int)s->it + 1);
             launches += 1;
+            if (two) IBLB_CUDA(cudaEventRecord(s->ev_b, sb));
         }
         LbParams qi = q;  // interior: never touches a ghost column
         qi.col_begin = G;
@@ -214,6 +229,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         qi.right.G = 0;
         rc = launch_lb(s, qi, st, launches);
         if (rc) return rc;
+        if (two) IBLB_CUDA(cudaEventRecord(s->ev_i, st));
     } else {
         int rc = launch_lb(s, q, st, launches);
         if (rc) return rc;
@@ -286,9 +302,12 @@ int check_device_flag(iblb_solver *s) {
     if (flag != 0) {
         set_error(flag == 1 ? "ib_tile_lists: more cilia overlap a tile than kBandMaxRel "
                               "(use IBLB_FLAG_NO_FUSE)"
-                            : "ib_tile_lists: more markers touch a tile than kTileCap "
-                              "(use IBLB_FLAG_NO_FUSE)");
-        return IBLB_EINVAL;
+                  : flag == 2 ? "ib_tile_lists: more markers touch a tile than kTileCap "
+                                "(use IBLB_FLAG_NO_FUSE)"
+                              : "slab_wait timed out: a neighbouring slab never reached this "
+                                "iteration (rank lost, or ranks stepped different counts); the "
+                                "state of this slab is no longer valid");
+        return flag == 3 ? IBLB_ECUDA : IBLB_EINVAL;
     }
     return IBLB_OK;
 }
@@ -308,6 +327,9 @@ int iblb_step(iblb_solver *s, unsigned n_steps) {
     s->pdl_chain = false;  // anything may have been enqueued since the last call
     IBLB_CUDA(cudaEventRecord(s->ev0, st));
     const bool coupled = s->connected && !(s->self_left && s->self_right);
+    const bool two = coupled && s->peer[0] == nullptr && s->stream_b != nullptr;
+    // the boundary stream starts behind everything enqueued on the main stream so far
+    if (two) IBLB_CUDA(cudaEventRecord(s->ev_i, st));
     // small grids are launch-bound: replay captured batches of kGraphBatch iterations (captured
     // with buffer A as the source: cur == 0)
     const long long nodes = (long long)s->L.W * s->L.YDIM;
@@ -346,6 +368,7 @@ int iblb_step(iblb_solver *s, unsigned n_steps) {
         if (rc) return rc;
         left--;
     }
+    if (two) IBLB_CUDA(cudaStreamWaitEvent(st, s->ev_b, 0));  // join: getters use the main stream
     IBLB_CUDA(cudaEventRecord(s->ev1, st));
     s->timed = true;
     s->last_launches = launches;

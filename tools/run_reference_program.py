@@ -213,6 +213,7 @@ def main():
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "refprog"))
     ap.add_argument("--no-timing", action="store_true")
     a = ap.parse_args()
+    a.out = os.path.abspath(a.out)
     if not os.path.exists(IBLB):
         print("oracle/_ref/IBLB not built (make -C oracle ref_bin)")
         return 1
