@@ -33,6 +33,20 @@ def _run(cmd):
     return r.stdout
 
 
+def build_checked(verbose=False):
+    """Development twin of the library with -DIBLB_CHECKED (device-side range checks on every index,
+    iblb_debug_violations() reports the count): cuda_iblb_11_b200/libiblb_checked.so, loaded instead
+    of libiblb.so when IBLB_LIB points at it (tools/sanitize_cases.py)."""
+    out = os.path.join(PKG, "libiblb_checked.so")
+    srcs = [os.path.join(CSRC, s) for s in CUDA_SOURCES + HOST_SOURCES]
+    cmd = ["nvcc", "-DIBLB_CHECKED", *ARCH, "-O3", "-lineinfo", "-std=c++17", "-shared", "-Xcompiler",
+           "-fPIC", "-I", os.path.join(ROOT, "include"), "-I", CSRC, "-o", out, *srcs, "-lcudart"]
+    log = _run(cmd)
+    if verbose:
+        print(log)
+    return out
+
+
 def build(force=False, verbose=False):
     """Compile libiblb.so and app if any source is newer.  Returns the library path."""
     headers = [os.path.join(CSRC, h) for h in ("iblb_device.cuh", "iblb_internal.h",
@@ -43,8 +57,6 @@ def build(force=False, verbose=False):
         cmd = ["nvcc", *ARCH, "-O3", "-lineinfo", "-std=c++17", "-shared", "-Xcompiler", "-fPIC",
                "-Xptxas", "-v", "-I", os.path.join(ROOT, "include"), "-I", CSRC,
                "-o", LIB, *srcs, "-lcudart"]
-        if os.environ.get("IBLB_TILE_TIMING"):  # development: per-CTA phase stamps
-            cmd.insert(1, "-DIBLB_TILE_TIMING")
         out = _run(cmd)
         if verbose:
             print(out)
@@ -56,4 +68,7 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose=True))
+    if "--checked" in sys.argv:
+        print(build_checked(verbose=True))
+    else:
+        print(build(force="--force" in sys.argv, verbose=True))

@@ -42,11 +42,13 @@ bool coupled(const iblb_solver *s) { return s->connected && !(s->self_left && s-
 // everything the state depends on; run length, output switches, device and the launch-mode flags
 // (graph / fusion / PDL) may differ
 bool same_params(const iblb_params &a, const iblb_params &b) {
-    const unsigned physics = IBLB_FLAG_HALF_FORCE_BODY | IBLB_FLAG_PICK_HIGHEST_K;
+    const unsigned physics = IBLB_FLAG_HALF_FORCE_BODY | IBLB_FLAG_PICK_HIGHEST_K | IBLB_FLAG_MUCUS;
     return a.c_fraction == b.c_fraction && a.c_num == b.c_num && a.c_space == b.c_space &&
            a.XDIM == b.XDIM && a.YDIM == b.YDIM && a.T == b.T && a.LENGTH == b.LENGTH &&
            a.p_step == b.p_step && a.TAU == b.TAU && a.TAU2 == b.TAU2 && a.gx == b.gx &&
            a.gy == b.gy && a.slab_x0 == b.slab_x0 && a.slab_w == b.slab_w &&
+           a.fine_points == b.fine_points && a.shape_scale == b.shape_scale &&
+           a.flux_back == b.flux_back &&
            (a.flags & physics) == (b.flags & physics);
 }
 
@@ -173,6 +175,8 @@ int iblb_load_checkpoint(iblb_solver *s, const char *path) {
     // completed iteration by the next getter (from the buffer that iteration pulled from)
     s->kin_base = -1;
     s->lists_base = -1;
+    if (s->tile_flag)  // iteration-numbered flags of the fused step: the iteration may have gone back
+        IBLB_CUDA(cudaMemset(s->tile_flag, 0, sizeof(int) * (size_t)s->band_tiles * s->tiles_x));
     s->pdl_chain = false;
     s->ib_stale = s->p.c_num > 0 && it > 0;
     return IBLB_OK;

@@ -1,66 +1,38 @@
 // One launch per iteration: immersed boundary and lattice Boltzmann in the same kernel.
 //
 //   every kKinBatch iterations   ib_kinematics_batch   markers: kinematics, epsilon, stencils  (ib_kernels.cu)
-//                                ib_tile_lists         per tile and iteration: the ascending list of
+//                                ib_tile_lists         per band tile and iteration: the ascending list of
 //                                                      markers whose 3x3 support can touch the tile
-//   every iteration              lb_ib_tile_step       F_s of the tile's markers -> spread -> pull-stream,
-//                                                      moments, TRT collide + Guo
+//   every iteration              lb_ib_tile_step       marker CTAs: F_s of a tile's markers -> the tile's force
+//                                                      LB CTAs: pull-stream, moments, TRT collide + Guo
 //
 // Replaces the reference's interpolate, spread, streaming, macro, equilibrium, collision launches
-// (ImmersedBoundary.cu:94-267, LatticeBoltzmann.cu:30-411).  A CTA owns a tile of 8 columns x 64
-// rows (warp = column, lane = row pair).  Everything about the markers that does not depend on the
-// fluid — positions, velocities, epsilon, delta factors AND which markers reach which tile — is
-// prescribed (main.cu:77-252 is a function of `it` alone) and is computed off the fluid's critical
-// path for a batch of iterations.  What is left per iteration is done by the tile that needs it: a
-// band tile computes F_s of the markers on its list straight from the post-collision populations
-// (nine support nodes x nine pulled populations each, ImmersedBoundary.cu:94-133; a marker that
-// reaches two tiles is evaluated by both: no inter-CTA dependency, no second launch, no atomics),
-// then every node sums its spreading terms in ascending marker order, the order of
-// ImmersedBoundary.cu:178-203.  Neither F_s nor the force goes through global memory: the force
-// is consumed by the collision of the same thread.  The LB loads are issued first, so their
-// latency hides behind the marker work.  Same device functions as lb_fused_v2 / ib_interp /
-// ib_spread: bit-identical results (tests/test_gpu_parity.py).
+// (ImmersedBoundary.cu:94-267, LatticeBoltzmann.cu:30-411).  A tile is 8 (or 6) columns x 64 rows
+// (warp = column, lane = row pair).  Everything about the markers that does not depend on the fluid
+// — positions, velocities, epsilon, delta factors AND which markers reach which tile — is prescribed
+// (main.cu:77-252 is a function of `it` alone) and is computed off the fluid's critical path for a
+// batch of iterations.  What is left per iteration is split between two kinds of CTA of ONE grid:
+//
+//   * marker CTAs (the lowest block indices, one per band tile that has markers): rho, u* of the
+//     support nodes straight from the post-collision populations (nine pulled populations each,
+//     ImmersedBoundary.cu:94-133), F_s of the markers on the tile's list (a marker that reaches two
+//     tiles is evaluated by both: no dependency between marker CTAs), every node of the tile sums
+//     its spreading terms in ascending marker order (ImmersedBoundary.cu:178-203), the tile's force
+//     goes to the band buffer and the tile's flag is released with the iteration number;
+//   * LB CTAs (every tile): issue their population loads, and — band tiles with markers only —
+//     acquire the tile's flag while those loads are in flight, read the two force values per node
+//     pair, collide, store.  They hold no shared memory and lb_fused_v2's registers.
+//
+// The marker chain (scattered pulls -> moments -> F_s -> spreading) therefore runs BESIDE the LB
+// tile's own load phase instead of in front of its collision, and the tiles without markers are as
+// light as the pure-LB kernel.  Lower block indices are dispatched first, so an LB CTA never waits
+// for a marker CTA that is not resident; the spin is bounded all the same.  Same device functions
+// as lb_fused_v2 / ib_interp / ib_spread: bit-identical results (tests/test_gpu_parity.py).
 #include "ib_device.cuh"
 #include "iblb_device.cuh"
 #include "lb_device.cuh"
 
 namespace iblb {
-
-// Development build (-DIBLB_TILE_TIMING): thread 0 of every CTA of lb_ib_tile_step stamps clock64()
-// at the phase boundaries into p.dbg[cta][16]; printed by iblb_destroy.  Not in product builds.
-#ifdef IBLB_TILE_TIMING
-#define TSTAMP(i)                                                                                  \
-    do {                                                                                           \
-        if (threadIdx.x == 0 && p.dbg)                                                             \
-            p.dbg[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 16 + (i)] = clock64();        \
-    } while (0)
-__device__ __forceinline__ unsigned long long gtime_ns() {
-    unsigned long long v;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(v));
-    return v;
-}
-// slot i: latest clock64 over the CTA's threads; slot i+2: latest globaltimer
-#define TSTAMP_MAX(i)                                                                              \
-    do {                                                                                           \
-        if (p.dbg) {                                                                               \
-            unsigned long long *d_ = (unsigned long long *)&p.dbg[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 16]; \
-            atomicMax(d_ + (i), (unsigned long long)clock64());                                    \
-            atomicMax(d_ + (i) + 2, gtime_ns());                                                   \
-        }                                                                                          \
-    } while (0)
-// CTA start: thread 0 clears the max slots and notes the global time
-#define TSTAMP_BEGIN()                                                                             \
-    do {                                                                                           \
-        if (threadIdx.x == 0 && p.dbg) {                                                           \
-            long long *d_ = &p.dbg[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 16];         \
-            d_[11] = 0; d_[12] = 0; d_[13] = 0; d_[14] = (long long)gtime_ns();                    \
-        }                                                                                          \
-    } while (0)
-#else
-#define TSTAMP(i)
-#define TSTAMP_MAX(i)
-#define TSTAMP_BEGIN()
-#endif
 
 namespace {
 
@@ -69,8 +41,6 @@ __device__ __forceinline__ void pdl_launch_dependents() {
     asm volatile("griddepcontrol.launch_dependents;");
 }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-
-constexpr int kTabX = 12, kTabY = 68;  // the tile's 8x64 nodes plus two rings around them
 
 struct TileMarkers {
     // the markers that can touch the tile: (F_x, F_y, bx, by), the 1-D delta factors of the columns
@@ -101,45 +71,17 @@ __device__ __forceinline__ int cta_rank(bool take, int *wcount, int &total) {
     return r;
 }
 
-// moment-table cell of ring node idx in [0, 4*kTabY + 4*tw) of a tile tw columns wide
-__device__ __forceinline__ int ring_cell(int idx, int tw) {
-    int lx, ly;
-    if (idx < 2 * kTabY) {  // two columns left of the tile
-        lx = idx / kTabY;
-        ly = idx - lx * kTabY;
-    } else if (idx < 4 * kTabY) {  // two columns right of it
-        const int r = idx - 2 * kTabY;
-        lx = r / kTabY;
-        ly = r - lx * kTabY;
-        lx += tw + 2;
-    } else {  // two rows below, two above
-        const int r = idx - 4 * kTabY;
-        const int row = r / tw;
-        lx = 2 + (r - row * tw);
-        ly = row < 2 ? row : 64 + row;
-    }
-    return lx * kTabY + ly;
-}
-
 // rho, u* of table cell c (a ring node, or an own node of a column past the channel), pulled from
 // global memory as the reference's interpolate would address it
 __device__ __forceinline__ void tile_pulled_cell(const Lattice &L, const double *__restrict__ src,
                                                  TileMarkers &sh, int tx0, int ty0, int c) {
+    IBLB_CHK(c >= 0 && c < kTabCells);
     const int lx = c / kTabY, ly = c - lx * kTabY;
     double rho, ux, uy;
     if (!support_node_moments(L, src, tx0 - 2 + lx, ty0 - 2 + ly, rho, ux, uy)) rho = ux = uy = 0.;
     sh.rho[c] = rho;
     sh.ux[c] = ux;
     sh.uy[c] = uy;
-}
-
-// rho and u* = sum c f / rho of pulled populations, same order as support_node_moments
-__device__ __forceinline__ void node_moments(const double (&f)[9], double &rho, double &ux,
-                                             double &uy) {
-    const double r = DA(DA(DA(DA(DA(DA(DA(DA(f[0], f[1]), f[2]), f[3]), f[4]), f[5]), f[6]), f[7]), f[8]);
-    rho = r;
-    ux = __ddiv_rn(DA(DS(DS(DA(DS(f[1], f[3]), f[5]), f[6]), f[7]), f[8]), r);
-    uy = __ddiv_rn(DS(DS(DA(DA(DS(f[2], f[4]), f[5]), f[6]), f[7]), f[8]), r);
 }
 
 // table cell of the centre of a marker's 3x3 support (ImmersedBoundary.cu:108-109: nearbyint of the
@@ -186,6 +128,7 @@ __device__ __forceinline__ void tile_marker_force(TileMarkers &sh, int tx0, int 
             const int cx = i == 0 ? 0 : i == 1 ? 1 : i == 2 ? 0 : i == 3 ? -1 : i == 4 ? 0 : (i == 5 || i == 8) ? 1 : -1;
             const int cy = i == 0 ? 0 : i == 1 ? 0 : i == 2 ? 1 : i == 3 ? 0 : i == 4 ? -1 : (i == 5 || i == 6) ? 1 : -1;
             const int c = c0 + cx * kTabY + cy;
+            IBLB_CHK(c >= 0 && c < kTabCells);
             const double rho = sh.rho[c];
             const float del = dx[cx + 1] * dy[cy + 1];  // float product (ImmersedBoundary.cu:78)
             // no branch (the nine terms overlap); a node off the array (rho = 0) contributes +0
@@ -302,6 +245,7 @@ __device__ __forceinline__ int build_spread_list(const TileMarkers &sh, SpreadLi
             const float ddx = wxs[4 * q + ix];
             const float wa = wys[4 * q + max(iy, 0)];
             const float wb = wys[4 * q + min(iy + 1, 3)];
+            IBLB_CHK(q >= 0 && q < kTileCap && ix >= 0 && ix <= 3 && iy >= -1 && iy <= 3 && t < 256);
             sl.d0[cnt][t] = iy >= 0 ? ddx * wa : 0.f;
             sl.d1[cnt][t] = iy <= 2 ? ddx * wb : 0.f;
             sl.q[cnt][t] = (unsigned short)q;
@@ -343,7 +287,7 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
     __shared__ int wcount[8];
     __shared__ int slist[kTileCap];
     __shared__ int2 sbase[kTileCap];
-    __shared__ unsigned char need[kTabX * kTabY];
+    __shared__ unsigned char need[kTabCells];
     const Lattice &L = p.lb.L;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int tile_y = blockIdx.x, tile_x = blockIdx.y, slot = blockIdx.z;
@@ -374,24 +318,25 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
         if (t == 0) {
             atomicExch(p.err, 1);
             pg.n = 0;
-            pg.nring = 0;
+            pg.ncell = 0;
         }
         return;
     }
     __syncthreads();
     int n = 0;
-    for (int c0 = 0; c0 < nrel * kMarkersPerCilium; c0 += 256) {
+    for (int c0 = 0; c0 < nrel * p.mpc; c0 += 256) {
         const int c = c0 + t;
         bool take = false;
         int k = 0;
-        if (c < nrel * kMarkersPerCilium) {
-            const int q = c / kMarkersPerCilium;
-            k = rel[q] * kMarkersPerCilium + (c - q * kMarkersPerCilium);
+        if (c < nrel * p.mpc) {
+            const int q = c / p.mpc;
+            k = rel[q] * p.mpc + (c - q * p.mpc);
             const float2 sm = ms[k];
             take = (meps[k] != 0) && sm.x >= xlo && sm.x <= xhi && sm.y >= ylo && sm.y <= yhi;
         }
         int total;
         const int r = n + cta_rank(take, wcount, total);
+        IBLB_CHK(!take || (k >= 0 && k < p.Ns));
         if (take && r < kTileCap) slist[r] = k;
         n += total;
     }
@@ -399,7 +344,7 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
         if (t == 0) atomicExch(p.err, 2);
         n = 0;
     }
-    for (int c = t; c < kTabX * kTabY; c += 256) need[c] = 0;
+    for (int c = t; c < kTabCells; c += 256) need[c] = 0;
     __syncthreads();
     for (int e = t; e < n; e += 256) {
         const int k = slist[e];
@@ -419,171 +364,138 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
 #pragma unroll
     for (int w = 0; w < kHitWords; w++)
         pg.hit[w][t] = w * 32 < n ? hit_mask32(sbase, w * 32, n, tx0 + warp, ty0 + 2 * lane) : 0u;
-    {
-        const int c = (warp + 2) * kTabY + 2 * lane + 2;
-        pg.own[t] = (unsigned char)((need[c] ? 1 : 0) | (need[c + 1] ? 2 : 0));
-    }
-    int nring = 0;
-    const int nring_all = 4 * kTabY + 4 * tw;
-    for (int i0 = 0; i0 < nring_all; i0 += 256) {
+    // the support nodes (in the tile or in the two rings around it), as cells of the moment table
+    int ncell = 0;
+    for (int i0 = 0; i0 < kTabCells; i0 += 256) {
         const int idx = i0 + t;
-        const bool take = idx < nring_all && need[ring_cell(idx, tw)] != 0;
+        const bool take = idx < kTabCells && need[idx] != 0;
         int total;
-        const int r = nring + cta_rank(take, wcount, total);
-        if (take) pg.ring[r] = (short)idx;
-        nring += total;
+        const int r = ncell + cta_rank(take, wcount, total);
+        IBLB_CHK(!take || (r >= 0 && r < kTabCells));
+        if (take) pg.cells[r] = (short)idx;
+        ncell += total;
     }
     if (t == 0) {
         pg.n = n;
-        pg.nring = nring;
+        pg.ncell = ncell;
     }
 }
 
-// grid = (row tiles, ceil(W/8)), block = 256.  Requires YDIM % 64 == 0 and a solver that owns the
-// whole channel (ghost columns = its own opposite edge).  Row tiles >= band_rows/64 are plain LB;
-// on tall grids only the band tiles are launched here and lb_fused_v2 takes the rows above.
-// p.M and p.prog point at the iteration's slot.
-__global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];  // kTileSmemBytes, dynamic
+namespace {
+
+__device__ __forceinline__ int ld_acquire_gpu(const int *p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(int *p, int v) {
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Marker CTA of band tile `tile`: the tile's force of this iteration into the band buffer.
+__device__ __forceinline__ void marker_cta(const BandParams &p, unsigned char *smem_raw, int tile) {
     TileMarkers &sh = *reinterpret_cast<TileMarkers *>(smem_raw);
     SpreadLists &sl = *reinterpret_cast<SpreadLists *>(smem_raw + sizeof(TileMarkers));
     const LbParams &lp = p.lb;
     const Lattice &L = lp.L;
-    const int tile_y = blockIdx.x, tile_x = blockIdx.y;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const int tw = p.tw, NT = tw * 32;  // columns per tile = warps of this CTA; threads
+    const int tw = p.tw, NT = tw * 32;
+    const int tile_y = tile / p.tiles_x, tile_x = tile - tile_y * p.tiles_x;
     const int tx0 = tile_x * tw, ty0 = tile_y * 64;
-    const int x = tx0 + warp;
-    const int y0 = ty0 + 2 * lane;
-    const bool active = x < L.W;  // warp-uniform
-    const bool band_tile = ty0 < p.band_rows;  // block-uniform
-    TSTAMP(0);
-    TSTAMP_BEGIN();
-
-    // Programmatic dependent launch: the next iteration's CTAs may start as soon as every CTA of
-    // this one is running.  Everything up to pdl_wait() reads only the prescribed marker data (the
-    // tile's plan and its markers, written by kernels that completed before the first kernel of this
-    // PDL chain started), so it overlaps the tail of the previous iteration; pdl_wait() returns once
-    // the previous iteration has completed and its populations are visible.
-    pdl_launch_dependents();
-    int n = 0, nring = 0;
-    const TileProgram *__restrict__ pg = nullptr;
-    if (band_tile) {
-        pg = p.prog + ((long long)tile_y * p.tiles_x + tile_x);
-        n = __ldg(&pg->n);
-        nring = __ldg(&pg->nring);
-    }
-    int r0 = 0, r1 = 0, own = 0;
+    const int x = tx0 + warp, y0 = ty0 + 2 * lane;
+    const TileProgram *__restrict__ pg = p.prog + tile;
+    const int n = __ldg(&pg->n);
+    if (n == 0) return;  // nobody waits for a tile without markers
+    const int ncell = __ldg(&pg->ncell);
+    // ---- prologue: reads only the prescribed marker data (the tile's plan and its markers, written
+    // by kernels that completed before the first kernel of this PDL chain started), so it overlaps
+    // the tail of the previous iteration
     unsigned hit[kHitWords] = {0u, 0u, 0u, 0u};
-    if (n > 0) {  // block-uniform
-        int k0 = 0, k1 = 0;
-        if (t < n) k0 = __ldg(pg->list + t);
-        if (t + NT < n) k1 = __ldg(pg->list + t + NT);
-        if (t < nring) r0 = __ldg(pg->ring + t);
-        if (t + NT < nring) r1 = __ldg(pg->ring + t + NT);
-        own = __ldg(pg->own + t);
 #pragma unroll
-        for (int w = 0; w < kHitWords; w++)
-            if (w * 32 < n) hit[w] = __ldg(&pg->hit[w][t]);
-#pragma unroll
-        for (int r = 0; r < 2; r++) {
-            const int e = t + NT * r;
-            if (e < n) {
-                const int k = r ? k1 : k0;
-                const float2 sm = p.M.s[k], us = p.M.u_s[k];
-                const int2 b = p.M.base[k];
-                sh.su[e] = make_float4(sm.x, sm.y, us.x, us.y);
-                sh.fb[e] = make_float4(0.f, 0.f, __int_as_float(b.x), __int_as_float(b.y));
-                sh.wx[e] = p.M.wx[k];
-                sh.wy[e] = p.M.wy[k];
-            }
-        }
+    for (int w = 0; w < kHitWords; w++)
+        if (w * 32 < n) hit[w] = __ldg(&pg->hit[w][t]);
+    const int c_first = t < ncell ? (int)__ldg(pg->cells + t) : 0;
+    for (int e = t; e < n; e += NT) {
+        const int k = __ldg(pg->list + e);
+        IBLB_CHK(k >= 0 && k < p.Ns && e < kTileCap);
+        const float2 sm = p.M.s[k], us = p.M.u_s[k];
+        const int2 b = p.M.base[k];
+        sh.su[e] = make_float4(sm.x, sm.y, us.x, us.y);
+        sh.fb[e] = make_float4(0.f, 0.f, __int_as_float(b.x), __int_as_float(b.y));
+        sh.wx[e] = p.M.wx[k];
+        sh.wy[e] = p.M.wy[k];
     }
-    int nlist = 0;
-    if (n > 0) {
-        __syncthreads();  // the staged markers
-        nlist = build_spread_list(sh, sl, n, x + L.x0, y0, hit);
+    __syncthreads();  // the staged markers
+    const int nlist = build_spread_list(sh, sl, n, x + L.x0, y0, hit);
+    pdl_wait();  // the previous iteration has completed: its populations are visible
+    const int epoch = (p.it_ptr ? __ldcg(p.it_ptr) : 0) + p.it + 1;
+    // ---- rho, u* of the support nodes: one thread per node, nine independent pulls each
+    for (int i = t; i < ncell; i += NT)
+        tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, i == t ? c_first : (int)__ldg(pg->cells + i));
+    __syncthreads();
+    for (int e = t; e < n; e += NT) tile_marker_force(sh, tx0 + L.x0, ty0, tw, e);
+    __syncthreads();
+    double fx0 = 0., fy0 = 0., fx1 = 0., fy1 = 0.;
+    list_spread(sh, sl, nlist, fx0, fy0, fx1, fy1);
+    tile_spread(sh, n, x + L.x0, y0, hit, fx0, fy0, fx1, fy1);  // what did not fit the list
+    if (x < L.W) {
+        IBLB_CHK(y0 >= 0 && y0 + 1 < lp.band_ld && tile >= 0 && tile < p.n_marker);
+        double *bp = p.band_w + (long long)x * lp.band_ld + y0;
+        __stcg(reinterpret_cast<double2 *>(bp), make_double2(fx0, fx1));
+        __stcg(reinterpret_cast<double2 *>(bp + (long long)L.W * lp.band_ld), make_double2(fy0, fy1));
     }
+    __threadfence();
+    __syncthreads();
+    if (t == 0) st_release_gpu(p.tile_flag + tile, epoch);
+}
+
+// LB CTA of tile (tile_y, tile_x): lb_fused_v2's work on an 8x64 tile, plus — band tiles with
+// markers — the force the tile's marker CTA leaves in the band buffer.
+__device__ __forceinline__ void lb_cta(const BandParams &p, int b) {
+    const LbParams &lp = p.lb;
+    const Lattice &L = lp.L;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    // rows above the band first: by the time the band's tiles are dispatched on a grid of several
+    // waves the marker CTAs have had a head start
+    const int ry = b / p.tiles_x, tile_x = b - ry * p.tiles_x;
+    const int tile_y = p.rows_lb - 1 - ry;
+    const int x = tile_x * p.tw + warp;
+    const int y0 = tile_y * 64 + 2 * lane;
+    const bool band_tile = tile_y * 64 < p.band_rows;  // block-uniform
+    const int tile = tile_y * p.tiles_x + tile_x;
+    int n = 0;
+    if (band_tile) n = __ldg(&p.prog[tile].n);
     pdl_wait();
-    TSTAMP(1);
-#ifdef IBLB_TILE_TIMING
-    if (threadIdx.x == 0 && p.dbg) p.dbg[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 16 + 12] = (long long)gtime_ns();
-#endif
+    if (x >= L.W) return;  // warp-uniform: columns past the channel
     Pulled q;
-    if (active) load_pulled(L, lp.src, x, y0, lane, q);
-#ifdef IBLB_TILE_TIMING
-    if (threadIdx.x == 0 && p.dbg) p.dbg[((long long)blockIdx.y * gridDim.x + blockIdx.x) * 16 + 15] = n;
-#endif
-
-    // the support nodes in the two rings around the tile: the first 256 are pulled into registers
-    // now and turned into moments after this thread's own nodes, so that their latency overlaps
-    double rf[9] = {1., 0., 0., 0., 0., 0., 0., 0., 0.};
-    bool rvalid = false;
-    int rc0 = 0;
-    if (t < nring) {
-        rc0 = ring_cell(r0, tw);
-        const int lx = rc0 / kTabY, ly = rc0 - lx * kTabY;
-        rvalid = support_node_pull(L, lp.src, tx0 + L.x0 - 2 + lx, ty0 - 2 + ly, rf);
-    }
-    if (n > 0) {
-        if (t + NT < nring) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, ring_cell(r1, tw));
-        if (!active) {  // columns past the channel (W % 8 != 0): as the reference would address them
-            const int c = (warp + 2) * kTabY + 2 * lane + 2;
-            if (own & 1) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, c);
-            if (own & 2) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, c + 1);
-        }
-    }
-
-    TSTAMP(2);
-    double a[9], b[9];
-    if (active) shift_pulled(q, lane, a, b);
-    TSTAMP(3);
-
+    load_pulled(L, lp.src, x, y0, lane, q);
     double Fx0 = lp.gx, Fy0 = lp.gy, Fx1 = lp.gx, Fy1 = lp.gy;
     bool forced = (lp.gx != 0.0) | (lp.gy != 0.0);
     if (band_tile) forced = true;  // as the reference: spread's velocity update covers every node
     if (n > 0) {
-        if (active) {  // this thread's support nodes: moments of the populations it pulled anyway
-            const int c = (warp + 2) * kTabY + 2 * lane + 2;
-            // a warp with any support node forms both nodes' moments in every lane, without
-            // branches (the two divisions per node overlap); cells nobody needs are never read
-            if (__any_sync(0xffffffffu, own != 0)) {
-                double r0_, x0_, y0_, r1_, x1_, y1_;
-                node_moments(a, r0_, x0_, y0_);
-                node_moments(b, r1_, x1_, y1_);
-                sh.rho[c] = r0_; sh.ux[c] = x0_; sh.uy[c] = y0_;
-                sh.rho[c + 1] = r1_; sh.ux[c + 1] = x1_; sh.uy[c + 1] = y1_;
+        // the populations are on their way; meanwhile wait for the tile's force of THIS iteration
+        const int epoch = (p.it_ptr ? __ldcg(p.it_ptr) : 0) + p.it + 1;
+        if (lane == 0) {
+            const long long t0 = clock64();
+            while (ld_acquire_gpu(p.tile_flag + tile) < epoch) {
+                if (clock64() - t0 > (1ll << 32)) {  // ~2 s: never in a working launch
+                    atomicExch(p.err, 4);
+                    break;
+                }
             }
         }
-        if (t < nring) {
-            double rho, ux, uy;
-            node_moments(rf, rho, ux, uy);  // rf = (1, 0, ...) placeholder when !rvalid
-            sh.rho[rc0] = rvalid ? rho : 0.;
-            sh.ux[rc0] = rvalid ? ux : 0.;
-            sh.uy[rc0] = rvalid ? uy : 0.;
-        }
-        TSTAMP(4);
-        __syncthreads();
-        TSTAMP(5);
-        if (t < n) tile_marker_force(sh, tx0 + L.x0, ty0, tw, t);
-        if (t + NT < n) tile_marker_force(sh, tx0 + L.x0, ty0, tw, t + NT);
-        TSTAMP(6);
-        __syncthreads();
-        TSTAMP(7);
-        double fx0 = 0., fy0 = 0., fx1 = 0., fy1 = 0.;
-        list_spread(sh, sl, nlist, fx0, fy0, fx1, fy1);
-        tile_spread(sh, n, x + L.x0, y0, hit, fx0, fy0, fx1, fy1);  // what did not fit the list
-        Fx0 += fx0; Fy0 += fy0; Fx1 += fx1; Fy1 += fy1;
-        TSTAMP(8);
+        __syncwarp();
+        IBLB_CHK(y0 >= 0 && y0 + 1 < lp.band_ld && tile >= 0 && tile < p.n_marker);
+        const double *bp = lp.band + (long long)x * lp.band_ld + y0;
+        const double2 bx = __ldcg(reinterpret_cast<const double2 *>(bp));
+        const double2 by = __ldcg(reinterpret_cast<const double2 *>(bp + (long long)L.W * lp.band_ld));
+        Fx0 += bx.x; Fx1 += bx.y; Fy0 += by.x; Fy1 += by.y;
     }
-    if (!active) return;
+    double a[9], c[9];
+    shift_pulled(q, lane, a, c);
     const double ux0 = collide_node(a, Fx0, Fy0, forced, lp);
-    const double ux1 = collide_node(b, Fx1, Fy1, forced, lp);
-    TSTAMP(9);
-    store_pair(lp, x, y0, a, b);
-    TSTAMP(10);
-    TSTAMP_MAX(11);
-
+    const double ux1 = collide_node(c, Fx1, Fy1, forced, lp);
+    store_pair(lp, x, y0, a, c);
     // flux through x = XDIM-5 (ImmersedBoundary.cu:259-264), same slots and order as lb_fused_v2
     if (x == lp.xq && lp.qacc != nullptr) {
         double s = ux0 + ux1;
@@ -593,12 +505,29 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
     }
 }
 
+}  // namespace
+
+// grid = n_marker + rows_lb * tiles_x CTAs of 32*tw threads.  Requires YDIM % 64 == 0 and a solver
+// that owns the whole channel (ghost columns = its own opposite edge).  On tall grids rows_lb covers
+// the band only and lb_fused_v2 takes the rows above.  p.M and p.prog point at the iteration's slot.
+__global__ void __launch_bounds__(256, 3) lb_ib_tile_step(const BandParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];  // marker CTAs only
+    // Programmatic dependent launch: the next iteration's CTAs may start as soon as every CTA of
+    // this one is running; each role calls pdl_wait() before it touches the populations.
+    pdl_launch_dependents();
+    const int b = blockIdx.x;
+    if (b < p.n_marker) marker_cta(p, smem_raw, b);
+    else lb_cta(p, b - p.n_marker);
+}
+
 // dynamic shared memory of lb_ib_tile_step (above the 48 KB static limit: opt-in per device)
 size_t tile_step_smem_bytes() { return sizeof(TileMarkers) + sizeof(SpreadLists); }
 cudaError_t tile_step_prepare() {
     return cudaFuncSetAttribute(lb_ib_tile_step, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)tile_step_smem_bytes());
 }
+
+IBLB_CHECKED_COUNTER(checked_count_fused)
 
 // last node of a captured batch of iterations: the iteration counter the batch reads
 __global__ void it_advance(int *it_ptr, int by) {

@@ -18,6 +18,18 @@ __device__ __constant__ const double kB[7 * 2 * 3] = {
     -0.499, 0.423, 0.138,  0.125,  0.075,  0.067,  0.0,    -1.017, -0.276, -0.196, -0.037,
     0.025,  0.023, 0.0,    0.339,  -0.327, -0.114, -0.105, -0.057, -0.055};
 
+// main.cu:36-54, the "WITH MUCUS PRESENT" set the reference keeps commented out (IBLB_FLAG_MUCUS)
+__device__ __constant__ const double kAmucus[7 * 2 * 3] = {
+    -0.449, 0.130,  -0.169, 0.063,  -0.050, -0.040, -0.068, 2.076,  -0.003, 0.054,  0.007,
+    0.026,  0.022,  0.010,  -0.072, -1.502, 0.260,  -0.123, 0.011,  -0.009, 0.196,  -1.074,
+    -0.230, -0.305, -0.180, -0.069, 0.001,  -0.080, 0.658,  0.793,  -0.251, 0.049,  0.009,
+    0.023,  -0.111, 0.381,  0.331,  0.193,  0.082,  0.029,  0.002,  0.048};
+__device__ __constant__ const double kBmucus[7 * 2 * 3] = {
+    0.0,   -0.030, -0.093, 0.037,  0.062,  0.016,  -0.065, 0.0,   0.080,  -0.044, -0.017,
+    0.052, 0.007,  0.051,  0.0,    1.285,  -0.036, -0.244, -0.093, -0.137, 0.095,  0.0,
+    -0.298, 0.513, 0.004,  -0.222, 0.035,  -0.128, 0.0,    -1.034, 0.050,  0.143,  0.043,
+    0.098, -0.054, 0.0,    0.210,  -0.367, 0.009,  0.120,  -0.024, 0.102};
+
 #define IBLB_PI_REF 3.14159  // main.cu:29
 
 namespace {
@@ -29,17 +41,18 @@ __device__ __forceinline__ int beat_phase(int it, int m, int p_step, int T) {
 
 // main.cu:137-145 for one marker; cs[n-1] = (cos, sin)(n*2*PI*phase/T).  Explicit intrinsics: the
 // same bits in every kernel that inlines it (see lb_device.cuh).
-__device__ __forceinline__ float2 marker_pos(const float *cf, const double2 *cs, float offset) {
-    float sx = __dadd_rn(__dmul_rn(__dmul_rn(111., (double)cf[0]), 0.5), (double)offset);
-    float sy = __dmul_rn(__dmul_rn(111., (double)cf[1]), 0.5);
+__device__ __forceinline__ float2 marker_pos(const float *cf, const double2 *cs, float offset,
+                                             double scale) {
+    float sx = __dadd_rn(__dmul_rn(__dmul_rn(scale, (double)cf[0]), 0.5), (double)offset);
+    float sy = __dmul_rn(__dmul_rn(scale, (double)cf[1]), 0.5);
 #pragma unroll
     for (int n = 1; n < 7; n++) {
         const double tx = __fma_rn((double)cf[2 * n + 0], cs[n - 1].x,
                                    __dmul_rn((double)cf[14 + 2 * n + 0], cs[n - 1].y));
         const double ty = __fma_rn((double)cf[2 * n + 1], cs[n - 1].x,
                                    __dmul_rn((double)cf[14 + 2 * n + 1], cs[n - 1].y));
-        sx = __dadd_rn((double)sx, __dmul_rn(111., tx));
-        sy = __dadd_rn((double)sy, __dmul_rn(111., ty));
+        sx = __dadd_rn((double)sx, __dmul_rn(scale, tx));
+        sy = __dadd_rn((double)sy, __dmul_rn(scale, ty));
     }
     return make_float2(sx, sy);
 }
@@ -57,13 +70,14 @@ __device__ __forceinline__ double beat_trig(int t, int it, int m, int p_step, in
 // marker of cilium m; cs0/cs1: trig tables of iterations it and it-1
 __device__ __forceinline__ void marker_state(const float *cf, const double2 *cs0,
                                              const double2 *cs1, int m, int it, int c_space_i,
-                                             int c_num_i, int XDIM, float2 &s, float2 &v) {
+                                             int c_num_i, int XDIM, double scale, float2 &s,
+                                             float2 &v) {
     const double c_space = c_space_i, c_num = c_num_i;
     const float offset = 1. * (m - (c_num - 1) / 2.) * c_space;  // main.cu:105
-    const float2 b = marker_pos(cf, cs0, offset);
+    const float2 b = marker_pos(cf, cs0, offset, scale);
     v = make_float2(0.f, 0.f);
     if (it > 0) {
-        const float2 l = marker_pos(cf, cs1, offset);
+        const float2 l = marker_pos(cf, cs1, offset, scale);
         v.x = b.x - l.x;
         v.y = b.y - l.y;
     }

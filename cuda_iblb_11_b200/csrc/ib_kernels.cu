@@ -20,16 +20,17 @@ namespace iblb {
 // Per-marker shape coefficients a_n(arcl), b_n(arcl) (main.cu:109-135), once at create.
 // k_of_j[j]: the fine point that wins marker j (main.cu:158-172).  coef[j][0..13] = a_n[2n+c],
 // coef[j][14..27] = b_n[2n+c].  Float accumulators, double terms, as the reference.
-__global__ void ib_coef(const int *k_of_j, float *coef) {
+__global__ void ib_coef(const int *k_of_j, float *coef, int mpc, int fine_points, int mucus) {
     const int j = threadIdx.x;
-    if (j >= kMarkersPerCilium) return;
-    const float arcl = 1. * k_of_j[j] / kFinePoints;  // main.cu:100
+    if (j >= mpc) return;
+    const float arcl = 1. * k_of_j[j] / fine_points;  // main.cu:100
+    const double *A = mucus ? kAmucus : kA, *B = mucus ? kBmucus : kB;
     for (int n = 0; n < 7; n++)
         for (int c = 0; c < 2; c++) {
             float a = 0.f, b = 0.f;
             for (int pw = 0; pw < 3; pw++) {
-                a += kA[n + 14 * pw + 7 * c] * pow(arcl, pw + 1);
-                b += kB[n + 14 * pw + 7 * c] * pow(arcl, pw + 1);
+                a += A[n + 14 * pw + 7 * c] * pow(arcl, pw + 1);
+                b += B[n + 14 * pw + 7 * c] * pow(arcl, pw + 1);
             }
             coef[j * 28 + 2 * n + c] = a;
             coef[j * 28 + 14 + 2 * n + c] = b;
@@ -48,30 +49,31 @@ __global__ void ib_coef(const int *k_of_j, float *coef) {
 // kKinBatch iterations.
 __global__ void __launch_bounds__(1024) ib_kinematics_batch(const IbParams p) {
     __shared__ __align__(16) double trig[kMaxLeftCilia][24];  // slot 0 = own, e = cilium m-e
-    __shared__ float2 pos[kMaxLeftCilia][kMarkersPerCilium];
-    __shared__ float2 vel[kMarkersPerCilium];
-    __shared__ int closef[kMarkersPerCilium];
-    __shared__ float wgt[kMarkersPerCilium][8];
+    __shared__ float2 pos[kMaxLeftCilia][kMaxMarkersPerCilium];
+    __shared__ float2 vel[kMaxMarkersPerCilium];
+    __shared__ int closef[kMaxMarkersPerCilium];
+    __shared__ float wgt[kMaxMarkersPerCilium][8];
     __shared__ float red_min[4], red_max[4];
+    const int mpc = p.mpc;  // markers per cilium, <= kMaxMarkersPerCilium
     const int m = blockIdx.x, slot = blockIdx.y;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int it = (p.it_ptr ? *p.it_ptr : p.it) + p.it_off + slot;
     const int r_max = p.r_max < 1 ? 1 : p.r_max;  // cilia whose positions are needed
-    if (t < kMarkersPerCilium) closef[t] = 0;
+    if (t < mpc) closef[t] = 0;
     for (int idx = t; idx < r_max * 24; idx += 1024) {
         const int e = idx / 24, r = idx - e * 24;
         const int mm = (m - e < 0) ? (m - e + p.c_num) : (m - e);
         if (e == 0 || r < 12) trig[e][r] = beat_trig(r % 12, it - r / 12, mm, p.p_step, p.T);
     }
     __syncthreads();
-    for (int idx = t; idx < r_max * kMarkersPerCilium; idx += 1024) {
-        const int e = idx / kMarkersPerCilium, j = idx - e * kMarkersPerCilium;
+    for (int idx = t; idx < r_max * mpc; idx += 1024) {
+        const int e = idx / mpc, j = idx - e * mpc;
         const int mm = (m - e < 0) ? (m - e + p.c_num) : (m - e);
         float2 sm, v;
         // neighbours only need the position: their trig[e][12..23] is not filled, it = 0 skips it
         marker_state(p.coef + j * 28, reinterpret_cast<const double2 *>(trig[e]),
                      reinterpret_cast<const double2 *>(trig[e] + 12), mm, e == 0 ? it : 0,
-                     p.c_space, p.c_num, p.L.XDIM, sm, v);
+                     p.c_space, p.c_num, p.L.XDIM, p.scale, sm, v);
         if (p.replay != nullptr && j == p.replay_j && it >= 0 && it < p.replay_steps) {
             // the reference's racing marker exactly as a recorded run produced it (test hook)
             const float4 r = p.replay[(long long)it * p.c_num + mm];
@@ -84,27 +86,28 @@ __global__ void __launch_bounds__(1024) ib_kinematics_batch(const IbParams p) {
     __syncthreads();
     // ---- epsilon: any marker of the r_max-1 cilia to the left within 1 unit on both axes ----
     {
-        const int j = t % kMarkersPerCilium, part = t / kMarkersPerCilium;  // 10 scanners a marker
-        if (part < 10) {
+        const int j = t % mpc, part = t / mpc, nparts = 1024 / mpc;  // 10 scanners a marker at 96
+        if (part < nparts) {
             const float2 sm = pos[0][j];
             bool close = false;
-            for (int idx = part; idx < (r_max - 1) * kMarkersPerCilium; idx += 10) {
-                const float2 o = (&pos[1][0])[idx];
+            for (int idx = part; idx < (r_max - 1) * mpc; idx += nparts) {
+                const float2 o = pos[1 + idx / mpc][idx % mpc];
                 close |= (fabsf(o.x - sm.x) < 1) && (fabsf(o.y - sm.y) < 1);
             }
             if (close) closef[j] = 1;
         }
     }
     // ---- spreading stencil: columns bx..bx+3, rows by..by+3 and their 1-D delta factors ----
-    if (t < kMarkersPerCilium * 8) {
+    if (t < mpc * 8) {
         const int j = t >> 3, i = t & 7;
         const float2 sm = pos[0][j];
         const int bx = (int)ceilf(sm.x - 1.5f), by = (int)ceilf(sm.y - 1.5f);
         wgt[j][i] = (i < 4) ? delta_1d(fabsf((bx + i) - sm.x)) : delta_1d(fabsf((by + i - 4) - sm.y));
     }
     __syncthreads();
-    if (t < kMarkersPerCilium) {
-        const long long k = (long long)slot * p.Ns + m * kMarkersPerCilium + t;
+    if (t < mpc) {
+        const long long k = (long long)slot * p.Ns + m * mpc + t;
+        IBLB_CHK(slot >= 0 && slot < kKinBatch && m >= 0 && m < p.c_num);
         const float2 sm = pos[0][t];
         p.M.s[k] = sm;
         p.M.u_s[k] = vel[t];
@@ -115,8 +118,8 @@ __global__ void __launch_bounds__(1024) ib_kinematics_batch(const IbParams p) {
     }
     // bbox of the wrapped x positions (for the spreading tiles)
     if (t < 128) {
-        const float sx = (t < kMarkersPerCilium) ? pos[0][t].x : 0.f;
-        float lo = (t < kMarkersPerCilium) ? sx : 3.0e38f, hi = (t < kMarkersPerCilium) ? sx : -3.0e38f;
+        const float sx = (t < mpc) ? pos[0][t].x : 0.f;
+        float lo = (t < mpc) ? sx : 3.0e38f, hi = (t < mpc) ? sx : -3.0e38f;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
@@ -130,8 +133,8 @@ __global__ void __launch_bounds__(1024) ib_kinematics_batch(const IbParams p) {
     __syncthreads();
     if (t == 0)
         p.M.bbox[slot * p.c_num + m] =
-            make_float2(fminf(fminf(red_min[0], red_min[1]), red_min[2]),
-                        fmaxf(fmaxf(red_max[0], red_max[1]), red_max[2]));
+            make_float2(fminf(fminf(red_min[0], red_min[1]), fminf(red_min[2], red_min[3])),
+                        fmaxf(fmaxf(red_max[0], red_max[1]), fmaxf(red_max[2], red_max[3])));
 }
 
 // F_s of every marker (ImmersedBoundary.cu:94-133), the only per-marker work that needs the fluid:
@@ -161,8 +164,9 @@ __global__ void __launch_bounds__(256) ib_interp(const IbParams p) {
 // (double)(F_s*delta [float product]) * eps   (ImmersedBoundary.cu:196-197).
 __global__ void __launch_bounds__(256) ib_spread(const IbParams p) {
     __shared__ unsigned relmask[64];      // relevant cilia bitmap (c_num <= 2048)
-    __shared__ float4 list[kMarkersPerCilium];
+    __shared__ float4 list[kMaxMarkersPerCilium];
     __shared__ int wcount[4];
+    const int mpc = p.mpc;
     const Lattice &L = p.L;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int tx0 = blockIdx.x * kSpreadTileX, ty0 = blockIdx.y * kSpreadTileY;
@@ -193,8 +197,8 @@ __global__ void __launch_bounds__(256) ib_spread(const IbParams p) {
             // ordered compaction of this cilium's markers that can touch the tile
             bool take = false;
             float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (t < kMarkersPerCilium) {
-                const int k = mcil * kMarkersPerCilium + t;
+            if (t < mpc) {
+                const int k = mcil * mpc + t;
                 const float2 sm = p.M.s[k];
                 take = (p.M.eps[k] != 0) && sm.x >= xlo && sm.x <= xhi && sm.y >= ylo && sm.y <= yhi;
                 if (take) {
@@ -203,13 +207,15 @@ __global__ void __launch_bounds__(256) ib_spread(const IbParams p) {
                 }
             }
             const unsigned tk = __ballot_sync(0xffffffffu, take);
-            if (lane == 0 && warp < 3) wcount[warp] = __popc(tk);
+            if (lane == 0 && warp < 4) wcount[warp] = __popc(tk);
             __syncthreads();
-            const int n = wcount[0] + wcount[1] + wcount[2];
+            const int n = wcount[0] + wcount[1] + wcount[2] + wcount[3];
             if (take) {
                 int pos = __popc(tk & ((1u << lane) - 1u));
                 if (warp >= 1) pos += wcount[0];
                 if (warp >= 2) pos += wcount[1];
+                if (warp >= 3) pos += wcount[2];
+                IBLB_CHK(pos >= 0 && pos < kMaxMarkersPerCilium);
                 list[pos] = e;
             }
             __syncthreads();
@@ -226,9 +232,12 @@ __global__ void __launch_bounds__(256) ib_spread(const IbParams p) {
         }
     }
     if (xl < L.W && y < p.band_rows) {
+        IBLB_CHK(y < p.band_ld);
         p.band[(long long)xl * p.band_ld + y] = fx;
         p.band[(long long)(L.W + xl) * p.band_ld + y] = fy;
     }
 }
+
+IBLB_CHECKED_COUNTER(checked_count_ib)
 
 }  // namespace iblb

@@ -11,6 +11,28 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+// Development build (-DIBLB_CHECKED, `IBLB_CHECKED=1 python -m cuda_iblb_11_b200.build --force`): every
+// index the kernels form into the population buffers, the force band, the marker arrays and the
+// shared-memory tables is range-checked on the device; violations are counted per translation unit
+// and summed by iblb_debug_violations().  Stands in for compute-sanitizer, which is closed on the
+// GPU pool (profiles/r02_sanitizer_unavailable.md).  Product builds compile the checks away.
+#ifdef IBLB_CHECKED
+static __device__ unsigned long long g_iblb_bad;
+#define IBLB_CHK(cond)                                  \
+    do {                                                \
+        if (!(cond)) atomicAdd(&g_iblb_bad, 1ull);      \
+    } while (0)
+#define IBLB_CHECKED_COUNTER(fn)                                            \
+    unsigned long long fn() {                                               \
+        unsigned long long v = 0;                                           \
+        cudaMemcpyFromSymbol(&v, g_iblb_bad, sizeof v);                     \
+        return v;                                                           \
+    }
+#else
+#define IBLB_CHK(cond) do {} while (0)
+#define IBLB_CHECKED_COUNTER(fn) unsigned long long fn() { return 0; }
+#endif
+
 namespace iblb {
 
 // D2Q9 lattice of LatticeBoltzmann.cu:15-27, i = 0..8
@@ -18,8 +40,10 @@ __device__ __constant__ const int kCx[9] = {0, 1, 0, -1, 0, 1, -1, -1, 1};
 __device__ __constant__ const int kCy[9] = {0, 0, 1, 0, -1, 1, 1, -1, -1};
 
 constexpr double kCs = 0.57735;  // device sound speed, LatticeBoltzmann.cu:11 (not 1/sqrt(3))
-constexpr int kMarkersPerCilium = 96;   // main.cu:83
+constexpr int kMarkersPerCilium = 96;   // main.cu:83: the reference's value (run-time: IbParams::mpc)
+constexpr int kMaxMarkersPerCilium = 128;  // capacity of the per-cilium shared-memory tables
 constexpr int kFinePoints = 9600;       // main.cu:81
+constexpr double kShapeScale = 111.;    // main.cu:137-145
 constexpr int kSpreadTileX = 8, kSpreadTileY = 32;
 constexpr int kKinBatch = 32;      // iterations of marker kinematics computed per launch
 constexpr int kSlabFlags = 4;  // slab step counters: [0],[1] data ready from the left / right neighbour; [2],[3] their release
@@ -34,6 +58,9 @@ struct Lattice {
     int x0;         // global x of local column 0
     long long plane;  // doubles per population plane = (W + 2G)*ld
     __host__ __device__ long long off(int xl, int y) const {
+#ifdef __CUDA_ARCH__
+        IBLB_CHK(xl >= -G && xl < W + G && y >= 0 && y < ld);
+#endif
         return (long long)(xl + G) * ld + y;
     }
 };
@@ -80,7 +107,9 @@ struct IbParams {
     Lattice L;
     const double *src;       // populations the step pulls from
     MarkerArrays M;
-    const float *coef;       // [96][28] a_n(x,y), b_n(x,y), n = 0..6 per marker (main.cu:109-135)
+    const float *coef;       // [mpc][28] a_n(x,y), b_n(x,y), n = 0..6 per marker (main.cu:109-135)
+    int mpc;                 // markers per cilium (main.cu:83: 96)
+    double scale;            // filament length scale (main.cu:137-145: 111)
     int c_num, c_space, T, p_step;
     int it, it_off;          // iteration = (it_ptr ? *it_ptr : it) + it_off
     const int *it_ptr;       // when set, the iteration number lives on the device (CUDA graphs)
@@ -98,31 +127,38 @@ struct IbParams {
 constexpr int kBandMaxRel = 128;  // cilia whose bounding box may overlap one 8-column tile
 constexpr int kTileCap = 384;     // markers (epsilon != 0) whose support can touch one 8x64 tile
 constexpr int kHitWords = 4;      // precomputed 32-marker hit-mask words per thread
-constexpr int kRingNodes = 304;   // nodes of the two rings around an 8x64 tile (the widest)
+constexpr int kTabX = 12, kTabY = 68;  // a tile's 8x64 nodes plus two rings around them
+constexpr int kTabCells = kTabX * kTabY;
 
 // Everything about one band tile at one iteration that does not depend on the fluid (the cilia are
 // prescribed), written by ib_tile_lists for a batch of iterations, read by lb_ib_tile_step.
 struct TileProgram {
     int n;                        // markers (epsilon != 0) whose 3x3 support can touch the tile
-    int nring;                    // ring nodes that are support nodes of these markers
+    int ncell;                    // nodes in and around the tile that are support nodes of these
     int pad[2];
-    int list[kTileCap];           // their indices, ascending (the reference's summation order)
+    int list[kTileCap];           // the markers' indices, ascending (the reference's summation order)
     unsigned hit[kHitWords][256]; // per thread (node pair): which of list[32w..32w+31] force its nodes
-    short ring[kRingNodes];       // the needed ring nodes
-    unsigned char own[256];       // per thread: bit 0/1 = node y0 / y0+1 is a support node
+    short cells[kTabCells];       // the support nodes, as cells of the tile's moment table
 };
 static_assert(sizeof(TileProgram) % 16 == 0, "TileProgram alignment");
 
 struct BandParams {
     LbParams lb;
     MarkerArrays M;          // ib_tile_lists: slot 0; lb_ib_tile_step: the iteration's slot
-    int c_num, Ns;
+    int c_num, Ns, mpc;
     int band_rows;           // rows that can receive IB force (multiple of 64)
     int tw;                  // columns per tile (6 or 8) = warps per CTA of lb_ib_tile_step
     int tiles_x;             // column tiles = ceil(W/tw)
     TileProgram *prog;       // [slot][band row tile][column tile]
     int *err;                // set non-zero when a tile exceeds kBandMaxRel / kTileCap
-    long long *dbg;          // development timing stamps (IBLB_TILE_TIMING builds) or nullptr
+    // lb_ib_tile_step: the first n_marker CTAs evaluate the markers of one band tile each and leave
+    // the tile's force in the band buffer; the others are the LB tiles
+    double *band_w;          // the force band, written by the marker CTAs (lb.band reads it)
+    int *tile_flag;          // per band tile: (iteration + 1) whose force the band holds
+    const int *it_ptr;       // iteration = (it_ptr ? *it_ptr : 0) + it
+    int it;
+    int n_marker;            // band row tiles x column tiles
+    int rows_lb;             // row tiles the LB CTAs cover (all of them, or the band's on tall grids)
 };
 
 }  // namespace iblb

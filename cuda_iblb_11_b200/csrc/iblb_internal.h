@@ -27,13 +27,16 @@ __global__ void lb_init(const LbParams p, const double *rho_in, const double *u_
 __global__ void halo_push(const Lattice L, const double *buf, Remote left, Remote right);
 __global__ void lb_moments(const LbParams p, int streamed, int row0, int nrows, double *rho_out,
                            double *u_out, double *f_out, double *force_out);
-__global__ void ib_coef(const int *k_of_j, float *coef);
+__global__ void ib_coef(const int *k_of_j, float *coef, int mpc, int fine_points, int mucus);
 __global__ void ib_kinematics_batch(const IbParams p);
 __global__ void ib_interp(const IbParams p);
 __global__ void ib_spread(const IbParams p);
 __global__ void ib_tile_lists(const BandParams p);
 __global__ void lb_ib_tile_step(const BandParams p);
 __global__ void it_advance(int *it_ptr, int by);
+unsigned long long checked_count_lb();     // IBLB_CHECKED builds: index violations per
+unsigned long long checked_count_ib();     // translation unit (0 in product builds)
+unsigned long long checked_count_fused();
 constexpr size_t kStageDoubles = (size_t)16 << 20;  // 128 MB
 int stage_buffer(iblb_solver *s);  // lazily allocates s->stage_dev
 size_t tile_step_smem_bytes();
@@ -54,6 +57,8 @@ struct iblb_solver {
     unsigned it;               // completed iterations
     // IB
     int Ns;
+    int mpc, fine_points;      // markers / fine points per cilium (main.cu:81-83: 96 / 9600)
+    double shape_scale;        // main.cu:137-145: 111
     iblb::MarkerArrays M;
     float *coef;
     int *k_of_j_dev;
@@ -69,7 +74,7 @@ struct iblb_solver {
     iblb::TileProgram *prog;   // per slot and band tile: fluid-independent plan (ib_tile_lists)
     int tile_w;                // columns per tile of lb_ib_tile_step: 8, or 6 where that fills the SMs better
     int tiles_x, band_tiles;   // column tiles, band row tiles
-    long long *dbg_dev;        // development timing stamps (IBLB_TILE_TIMING builds)
+    int *tile_flag;            // per band tile: iteration + 1 whose force the band buffer holds
     long long lists_base;      // tile lists hold iterations [lists_base, lists_base + kKinBatch); -1: none
     float reach_x, reach_y;    // bounds on the marker excursion from the cilium base
     std::vector<float> env;    // per marker of a cilium: x lo, x hi, y lo, y hi over the beat cycle

@@ -97,6 +97,7 @@ __device__ __forceinline__ double collide_node(double (&f)[9], double Fx, double
 }
 
 __device__ __forceinline__ void store_remote2(const Remote &r, int col, int y0, int i, double2 v) {
+    IBLB_CHK(col + r.G >= 0 && col + r.G < r.W + 2 * r.G && y0 >= 0 && y0 + 1 < r.ld && i >= 0 && i < 9);
     *reinterpret_cast<double2 *>(r.base + (long long)i * r.plane + (long long)(col + r.G) * r.ld +
                                  y0) = v;
 }

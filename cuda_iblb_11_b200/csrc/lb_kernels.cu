@@ -41,6 +41,7 @@ __global__ void __launch_bounds__(256, 3) lb_fused_v2(const LbParams p) {
     double Fx0 = p.gx, Fy0 = p.gy, Fx1 = p.gx, Fy1 = p.gy;
     bool forced = (p.gx != 0.0) | (p.gy != 0.0);
     if (p.band != nullptr && y0 < p.band_rows) {  // warp-uniform: band_rows % 64 == 0
+        IBLB_CHK(x >= 0 && x < L.W && y0 >= 0 && y0 + 1 < p.band_ld);
         const double *b = p.band + (long long)x * p.band_ld + y0;
         const double2 bx = ldg2(b);
         const double2 by = ldg2(b + (long long)L.W * p.band_ld);
@@ -283,9 +284,7 @@ __global__ void lb_moments(const LbParams p, int streamed, int row0, int nrows, 
     }
 }
 
-}  // namespace iblb
-
-namespace iblb {
+IBLB_CHECKED_COUNTER(checked_count_lb)
 
 // ---- slab ordering across GPUs (one process per GPU): step counters in peer-mapped memory.
 // flags[0], flags[1]: "data ready" — the left / right neighbour has stored the boundary columns of

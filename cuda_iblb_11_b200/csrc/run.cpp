@@ -116,7 +116,8 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
     const unsigned XDIM = p.XDIM, YDIM = p.YDIM, c_num = p.c_num, c_fraction = p.c_fraction;
     const unsigned ITERATIONS = p.ITERATIONS, INTERVAL = p.INTERVAL;
     const size_t size = (size_t)XDIM * YDIM;
-    const int Ns = 96 * (int)c_num;
+    const int mpc = p.LENGTH ? (int)p.LENGTH : 96;  // markers per cilium (main.cu:83,442)
+    const int Ns = mpc * (int)c_num;
 
     // ---- directories, main.cu:589-613 (root is configurable; the reference hard-codes it) ----
     string output_data = root ? root : "Data/";
@@ -239,7 +240,7 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
                         f << sm[2 * k + 0] * x_scale << "\t" << sm[2 * k + 1] * x_scale << "\t"
                           << us[2 * k + 0] * s_scale << "\t" << us[2 * k + 1] * s_scale << "\t"
                           << eps[k] << "\n";
-                        if (k % 96 == 95 || sm[2 * k + 0] > XDIM - 1 || sm[2 * k + 0] < 1) f << "\n";
+                        if (k % mpc == mpc - 1 || sm[2 * k + 0] > XDIM - 1 || sm[2 * k + 0] < 1) f << "\n";
                     }
                     f.close();
                     return ok && !f.fail();

@@ -21,12 +21,14 @@ namespace {
 
 // which fine points can write marker j (main.cu:158-172 evaluated for every k in float, as the
 // kernel does); the winner of the write race is the lowest k (measured on B200) unless PICK_HIGHEST_K.
-void build_marker_table(std::vector<int> &k_of_j, bool lowest) {
-    k_of_j.assign(kMarkersPerCilium, -1);
-    for (int k = 0; k < kFinePoints; k++) {
-        const float arcl = 1. * k / kFinePoints;  // main.cu:100
-        const float s2 = 111 * arcl;              // main.cu:139
-        for (int j = 0; j < kMarkersPerCilium; j++) {
+void build_marker_table(std::vector<int> &k_of_j, bool lowest, int mpc, int fine_points,
+                        double scale) {
+    k_of_j.assign(mpc, -1);
+    for (int k = 0; k < fine_points; k++) {
+        const float arcl = 1. * k / fine_points;  // main.cu:100
+        const float s2 = scale * arcl;            // main.cu:139 (the product of two floats is exact
+                                                  // in double: same bits as the float multiply)
+        for (int j = 0; j < mpc; j++) {
             const float b_length = j;
             if (fabsf(s2 - b_length) < 0.01) {
                 if (k_of_j[j] < 0 || !lowest) k_of_j[j] = k;
@@ -96,7 +98,9 @@ IbParams make_ib_params(const iblb_solver *s, int src_idx, int slot) {
     q.it_off = 0;
     q.it_ptr = nullptr;
     q.Ns = s->Ns;
-    q.r_max = (int)(2 * kMarkersPerCilium / (double)s->p.c_space);  // main.cu:185
+    q.mpc = s->mpc;
+    q.scale = s->shape_scale;
+    q.r_max = (int)(2 * s->mpc / (double)s->p.c_space);  // main.cu:185
     q.band = s->band;
     q.band_rows = s->band_rows;
     q.band_ld = s->band_ld;
@@ -150,6 +154,8 @@ static int init_state(iblb_solver *s, const double *rho, const double *u) {
     if (s->band) IBLB_CUDA(cudaMemsetAsync(s->band, 0, sizeof(double) * 2 * s->L.W * s->band_ld, s->stream));
     IBLB_CUDA(cudaMemsetAsync(s->qacc, 0, sizeof(double) * s->nq, s->stream));
     if (s->it_dev) IBLB_CUDA(cudaMemsetAsync(s->it_dev, 0, sizeof(int), s->stream));
+    if (s->tile_flag)  // the tiles' force flags carry iteration numbers, which start over
+        IBLB_CUDA(cudaMemsetAsync(s->tile_flag, 0, sizeof(int) * (size_t)s->band_tiles * s->tiles_x, s->stream));
     s->cur = 0;
     s->ib_stale = false;
     s->kin_base = -1;
@@ -173,10 +179,23 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
         set_error("iblb_create: XDIM, YDIM must be >= 4 and YDIM even");
         return IBLB_EINVAL;
     }
-    if (p.c_num > 0 && (p.XDIM != p.c_num * p.c_space || p.c_num > 2048 || p.YDIM < 128 ||
-                        2 * kMarkersPerCilium / (int)p.c_space > kMaxLeftCilia)) {
+    // cilium geometry: the reference's hard-wired values unless the caller gives others
+    const int mpc = p.LENGTH ? (int)p.LENGTH : kMarkersPerCilium;
+    const int fine_points = p.fine_points ? (int)p.fine_points : kFinePoints;
+    const double shape_scale = p.shape_scale > 0. ? p.shape_scale : kShapeScale;
+    const int flux_back = p.flux_back ? (int)p.flux_back : 5;
+    if (p.c_num > 0 && (p.XDIM != p.c_num * p.c_space || p.c_num > 2048 || p.c_space == 0 ||
+                        2 * mpc / (int)p.c_space > kMaxLeftCilia)) {
         set_error("iblb_create: with cilia XDIM must equal c_num*c_space, c_num <= 2048, "
-                  "YDIM >= 128, c_space >= 12");
+                  "2*LENGTH/c_space <= 16");
+        return IBLB_EINVAL;
+    }
+    if (p.c_num > 0 && (mpc < 1 || mpc > kMaxMarkersPerCilium || fine_points < mpc)) {
+        set_error("iblb_create: LENGTH (markers per cilium) must be 1..128 and fine_points >= LENGTH");
+        return IBLB_EINVAL;
+    }
+    if (flux_back < 1 || flux_back > (int)p.XDIM) {
+        set_error("iblb_create: flux_back must be in 1..XDIM");
         return IBLB_EINVAL;
     }
     if (!(p.TAU > 0.5) || !(p.TAU2 > 0.5)) {
@@ -212,7 +231,10 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
         return IBLB_EINVAL;
     }
     s->vec2 = (p.YDIM % 64 == 0);
-    s->Ns = kMarkersPerCilium * (int)p.c_num;
+    s->mpc = mpc;
+    s->fine_points = fine_points;
+    s->shape_scale = shape_scale;
+    s->Ns = mpc * (int)p.c_num;
 
     int rc = IBLB_OK;
 #define TRY(call)                                   \
@@ -243,9 +265,6 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
     TRY(cudaEventCreate(&s->ev0));
     TRY(cudaEventCreate(&s->ev1));
     if (p.c_num > 0 && rc == IBLB_OK) {
-        s->band_rows = 128;
-        s->band_ld = 128;
-        TRY(cudaMalloc((void **)&s->band, sizeof(double) * 2 * (size_t)L.W * s->band_ld));
         // marker arrays: kKinBatch iteration slots (stride Ns); F_s only for the current iteration
         const size_t nm = (size_t)s->Ns * kKinBatch;
         TRY(cudaMalloc((void **)&s->M.s, sizeof(float2) * nm));
@@ -256,22 +275,33 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
         TRY(cudaMalloc((void **)&s->M.wx, sizeof(float4) * nm));
         TRY(cudaMalloc((void **)&s->M.wy, sizeof(float4) * nm));
         TRY(cudaMalloc((void **)&s->M.base, sizeof(int2) * nm));
-        TRY(cudaMalloc((void **)&s->coef, sizeof(float) * kMarkersPerCilium * 28));
-        TRY(cudaMalloc((void **)&s->k_of_j_dev, sizeof(int) * kMarkersPerCilium));
+        TRY(cudaMalloc((void **)&s->coef, sizeof(float) * mpc * 28));
+        TRY(cudaMalloc((void **)&s->k_of_j_dev, sizeof(int) * mpc));
         if (rc == IBLB_OK) {
             TRY(cudaMemset(s->M.s, 0, sizeof(float2) * nm));
             TRY(cudaMemset(s->M.u_s, 0, sizeof(float2) * nm));
             TRY(cudaMemset(s->M.F_s, 0, sizeof(float2) * s->Ns));
             TRY(cudaMemset(s->M.eps, 0, sizeof(int) * nm));
-            build_marker_table(s->k_of_j, (p.flags & IBLB_FLAG_PICK_HIGHEST_K) == 0);
-            TRY(cudaMemcpy(s->k_of_j_dev, s->k_of_j.data(), sizeof(int) * kMarkersPerCilium,
+            build_marker_table(s->k_of_j, (p.flags & IBLB_FLAG_PICK_HIGHEST_K) == 0, mpc,
+                               fine_points, shape_scale);
+            for (int j = 0; j < mpc && rc == IBLB_OK; j++)
+                if (s->k_of_j[j] < 0) {
+                    // main.cu:158-172 would leave this marker at the origin for ever
+                    set_error("iblb_create: no fine point falls on marker " + std::to_string(j) +
+                              " (|shape_scale*k/fine_points - j| < 0.01 has no solution)");
+                    rc = IBLB_EINVAL;
+                }
+        }
+        if (rc == IBLB_OK) {
+            TRY(cudaMemcpy(s->k_of_j_dev, s->k_of_j.data(), sizeof(int) * mpc,
                            cudaMemcpyHostToDevice));
-            ib_coef<<<1, 128, 0, s->stream>>>(s->k_of_j_dev, s->coef);
+            ib_coef<<<1, 128, 0, s->stream>>>(s->k_of_j_dev, s->coef, mpc, fine_points,
+                                              (p.flags & IBLB_FLAG_MUCUS) ? 1 : 0);
             TRY(cudaGetLastError());
             // envelope of every marker over the whole beat cycle, relative to its cilium's base
             // (main.cu:137-145): sampled at kEnvSamples phases, widened by the distance a marker can
             // move between two samples (bound on d/dphase from the coefficients) — rigorous
-            std::vector<float> cf(kMarkersPerCilium * 28);
+            std::vector<float> cf((size_t)mpc * 28);
             TRY(cudaMemcpyAsync(cf.data(), s->coef, sizeof(float) * cf.size(),
                                 cudaMemcpyDeviceToHost, s->stream));
             TRY(cudaStreamSynchronize(s->stream));
@@ -283,18 +313,18 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
                     cs[k * 12 + 2 * (n - 1)] = cos(n * two_pi * k / kEnvSamples);
                     cs[k * 12 + 2 * (n - 1) + 1] = sin(n * two_pi * k / kEnvSamples);
                 }
-            s->env.assign(4 * kMarkersPerCilium, 0.f);
+            s->env.assign(4 * (size_t)mpc, 0.f);
             double rx = 0., ry = 0.;
-            for (int j = 0; j < kMarkersPerCilium && rc == IBLB_OK; j++) {
+            for (int j = 0; j < mpc && rc == IBLB_OK; j++) {
                 const float *c = cf.data() + j * 28;
                 double lo[2] = {1e30, 1e30}, hi[2] = {-1e30, -1e30}, lip[2] = {0., 0.};
                 for (int a = 0; a < 2; a++) {
                     for (int n = 1; n < 7; n++)
-                        lip[a] += 111. * n * two_pi * hypot((double)c[2 * n + a], (double)c[14 + 2 * n + a]);
+                        lip[a] += shape_scale * n * two_pi * hypot((double)c[2 * n + a], (double)c[14 + 2 * n + a]);
                     for (int k = 0; k < kEnvSamples; k++) {
-                        double v = 111. * c[a] * 0.5;
+                        double v = shape_scale * c[a] * 0.5;
                         for (int n = 1; n < 7; n++)
-                            v += 111. * (c[2 * n + a] * cs[k * 12 + 2 * (n - 1)] +
+                            v += shape_scale * (c[2 * n + a] * cs[k * 12 + 2 * (n - 1)] +
                                          c[14 + 2 * n + a] * cs[k * 12 + 2 * (n - 1) + 1]);
                         lo[a] = v < lo[a] ? v : lo[a];
                         hi[a] = v > hi[a] ? v : hi[a];
@@ -312,6 +342,17 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
             }
             s->reach_x = (float)rx;
             s->reach_y = (float)ry;
+            // the force band: the rows a marker's delta support can ever reach, in whole row tiles
+            // (the reference's cilia stay below y = 96: two tiles)
+            s->band_rows = 64 * (int)((ry + 1.5 + 1. + 63.) / 64.);
+            s->band_ld = s->band_rows;
+            if (s->band_rows > (int)p.YDIM && rc == IBLB_OK) {
+                set_error("iblb_create: the cilia reach y = " + std::to_string(ry) +
+                          ": YDIM must be at least " + std::to_string(s->band_rows));
+                rc = IBLB_EINVAL;
+            }
+            if (rc == IBLB_OK)
+                TRY(cudaMalloc((void **)&s->band, sizeof(double) * 2 * (size_t)L.W * s->band_ld));
         }
     }
 #undef TRY
@@ -323,7 +364,7 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
     }
     // flux plane x = XDIM-5 (ImmersedBoundary.cu:259); accumulated only where `spread` runs in
     // the reference (cilia present) or the half-force extension asks for it
-    const int xq = (int)p.XDIM - 5 - L.x0;
+    const int xq = (int)p.XDIM - flux_back - L.x0;
     s->xq_local = xq;
     s->flux_on = (p.c_num > 0 || (p.flags & IBLB_FLAG_HALF_FORCE_BODY)) && xq >= 0 && xq < L.W;
     // spreading fused into the LB kernel: whole channel on this GPU, vector path; in every mode the
@@ -370,7 +411,7 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
                 std::vector<int> cnt((size_t)ntx * nty, 0), ccnt((size_t)ntx, 0), seen((size_t)ntx, -1);
                 for (int m = 0; m < (int)p.c_num; m++) {
                     const double base = (double)p.c_space * (m + 0.5);
-                    for (int j = 0; j < kMarkersPerCilium; j++) {
+                    for (int j = 0; j < mpc; j++) {
                         const double xl = base + s->env[4 * j] - 1.5, xh = base + s->env[4 * j + 1] + 1.5;
                         const double yl = s->env[4 * j + 2] - 1.5, yh = s->env[4 * j + 3] + 1.5;
                         const int ty_lo = std::max(0, (int)floor(yl / 64.)), ty_hi = std::min(nty - 1, (int)floor(yh / 64.));
@@ -396,11 +437,9 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
             cudaError_t e = tile_step_prepare();
             if (e == cudaSuccess) e = cudaMalloc((void **)&s->prog, sizeof(TileProgram) * nt);
             if (e == cudaSuccess) e = cudaMemset(s->prog, 0, sizeof(TileProgram) * nt);
-#ifdef IBLB_TILE_TIMING
-            const size_t nd = (size_t)(L.YDIM / 64) * s->tiles_x * 16;
-            if (e == cudaSuccess) e = cudaMalloc((void **)&s->dbg_dev, sizeof(long long) * nd);
-            if (e == cudaSuccess) e = cudaMemset(s->dbg_dev, 0, sizeof(long long) * nd);
-#endif
+            const size_t nf = sizeof(int) * (size_t)s->band_tiles * s->tiles_x;
+            if (e == cudaSuccess) e = cudaMalloc((void **)&s->tile_flag, nf);
+            if (e == cudaSuccess) e = cudaMemset(s->tile_flag, 0, nf);
             if (e != cudaSuccess) {
                 iblb_destroy(s);
                 return cuda_fail(e, "cudaMalloc(tile lists)");
@@ -433,45 +472,6 @@ int iblb_destroy(iblb_solver *s) {
     if (!s) return IBLB_OK;
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
-#ifdef IBLB_TILE_TIMING
-    if (s->dbg_dev) {  // phase stamps of the last lb_ib_tile_step launch, per CTA
-        const int ty = s->L.YDIM / 64 > 8 ? s->band_tiles : s->L.YDIM / 64;
-        const size_t nc = (size_t)ty * s->tiles_x;
-        std::vector<long long> h(nc * 16);
-        cudaMemcpy(h.data(), s->dbg_dev, sizeof(long long) * nc * 16, cudaMemcpyDeviceToHost);
-        size_t worst = 0;
-        // slots: 0..10 clock64 of thread 0 at the phase boundaries, 11 latest clock64 at exit over
-        // the CTA's threads, 12 globaltimer at wait return, 13 latest globaltimer at exit,
-        // 14 globaltimer at CTA start, 15 markers of the tile
-        double avg[12] = {0};
-        for (size_t c = 0; c < nc; c++) {
-            if (h[c * 16 + 13] - h[c * 16 + 12] > h[worst * 16 + 13] - h[worst * 16 + 12]) worst = c;
-            for (int i = 1; i <= 11; i++) avg[i] += (double)(h[c * 16 + i] - h[c * 16]) / nc;
-        }
-        fprintf(stderr, "tile timing (%zu CTAs), cycles since CTA start: avg", nc);
-        for (int i = 1; i <= 11; i++) fprintf(stderr, " %.0f", avg[i]);
-        fprintf(stderr, "\n  longest CTA after the wait %zu (n=%lld):", worst, h[worst * 16 + 15]);
-        for (int i = 1; i <= 11; i++) fprintf(stderr, " %lld", h[worst * 16 + i] - h[worst * 16]);
-        long long t0 = h[14], tw0 = h[12], tw1 = 0, t1 = 0;
-        for (size_t c = 0; c < nc; c++) {
-            if (h[c * 16 + 14] < t0) t0 = h[c * 16 + 14];
-            if (h[c * 16 + 12] < tw0) tw0 = h[c * 16 + 12];
-            if (h[c * 16 + 12] > tw1) tw1 = h[c * 16 + 12];
-            if (h[c * 16 + 13] > t1) t1 = h[c * 16 + 13];
-        }
-        double a0 = 0, a1 = 0; int c0n = 0, c1n = 0; long long m0 = 0, m1 = 0;
-        for (size_t c = 0; c < nc; c++) {
-            const long long d = h[c * 16 + 13] - h[c * 16 + 12];
-            if (h[c * 16 + 15] > 0) { a1 += d; c1n++; if (d > m1) m1 = d; }
-            else { a0 += d; c0n++; if (d > m0) m0 = d; }
-        }
-        fprintf(stderr, "\n  ns from wait return to last thread exit: %d tiles without markers avg %.0f max %lld, %d with markers avg %.0f max %lld",
-                c0n, c0n ? a0 / c0n : 0., m0, c1n, c1n ? a1 / c1n : 0., m1);
-        fprintf(stderr, "\n  grid, ns since the first CTA start: wait returns %lld..%lld, last exit %lld\n",
-                tw0 - t0, tw1 - t0, t1 - t0);
-        cudaFree(s->dbg_dev);
-    }
-#endif
     if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
     cudaFree(s->err_dev);
     for (int f = 0; f < 2; f++) {
@@ -487,6 +487,7 @@ int iblb_destroy(iblb_solver *s) {
     cudaFree(s->M.wx); cudaFree(s->M.wy); cudaFree(s->M.base);
     cudaFree(s->k_of_j_dev); cudaFree(s->it_dev);
     cudaFree(s->prog);
+    cudaFree(s->tile_flag);
     cudaFree(s->replay_dev);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -517,11 +518,23 @@ int iblb_sync(iblb_solver *s) {
 
 unsigned iblb_iteration(const iblb_solver *s) { return s ? s->it : 0; }
 
+// Development: index violations counted on the device by an IBLB_CHECKED build (all solvers of the
+// current device, since start); -1 when the library was built without the checks.
+long long iblb_debug_violations(void) {
+#ifdef IBLB_CHECKED
+    cudaDeviceSynchronize();
+    return (long long)(checked_count_lb() + checked_count_ib() + checked_count_fused());
+#else
+    return -1;
+#endif
+}
+
 int iblb_marker_fine_index(const iblb_solver *s, unsigned j) {
-    if (!s || j >= (unsigned)kMarkersPerCilium) return -1;
+    if (!s || j >= (unsigned)s->mpc) return -1;
     if (s->k_of_j.empty()) {
         std::vector<int> t;
-        build_marker_table(t, (s->p.flags & IBLB_FLAG_PICK_HIGHEST_K) == 0);
+        build_marker_table(t, (s->p.flags & IBLB_FLAG_PICK_HIGHEST_K) == 0, s->mpc, s->fine_points,
+                           s->shape_scale);
         return t[j];
     }
     return s->k_of_j[j];
@@ -533,7 +546,7 @@ int iblb_marker_fine_index(const iblb_solver *s, unsigned j) {
 // values a recorded run of the reference produced, the product can be compared with that run
 // directly at the stated tolerance (tests/test_gpu_parity.py).
 int iblb_set_marker_replay(iblb_solver *s, unsigned marker_j, const float *vals, unsigned n_steps) {
-    if (!s || s->p.c_num == 0 || marker_j >= (unsigned)kMarkersPerCilium) {
+    if (!s || s->p.c_num == 0 || marker_j >= (unsigned)s->mpc) {
         set_error("iblb_set_marker_replay: bad argument");
         return IBLB_EINVAL;
     }

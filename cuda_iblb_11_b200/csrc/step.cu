@@ -22,16 +22,21 @@ BandParams make_band_params(const iblb_solver *s, int src_idx, int slot) {
     BandParams q;
     memset(&q, 0, sizeof q);
     q.lb = make_lb_params(s, src_idx);
-    q.lb.band = nullptr;  // the force never goes through memory
     q.M = marker_slot(s, slot);
     q.c_num = (int)s->p.c_num;
     q.Ns = s->Ns;
+    q.mpc = s->mpc;
     q.band_rows = s->band_rows;
     q.tw = s->tile_w;
     q.tiles_x = s->tiles_x;
     q.prog = s->prog + (size_t)slot * s->band_tiles * s->tiles_x;
     q.err = s->err_dev;
-    q.dbg = s->dbg_dev;
+    q.band_w = s->band;
+    q.tile_flag = s->tile_flag;
+    q.it_ptr = nullptr;
+    q.it = (int)s->it;
+    q.n_marker = s->band_tiles * s->tiles_x;
+    q.rows_lb = s->L.YDIM / 64;
     return q;
 }
 
@@ -176,11 +181,16 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         BandParams bp = make_band_params(s, src, slot);
         const int tiles_y = s->L.YDIM / 64, band_tiles = s->band_rows / 64;
         // short channels: one launch for all row tiles; tall ones: band tiles here, the rest in
-        // lb_fused_v2 (leaner: no shared memory, 3 CTAs per SM)
+        // lb_fused_v2
         const bool split = tiles_y > 8;
-        dim3 g((unsigned)(split ? band_tiles : tiles_y), (unsigned)s->tiles_x);
+        bp.rows_lb = split ? band_tiles : tiles_y;
+        if (graph_mode) {  // the iteration number lives on the device (see build_graph)
+            bp.it_ptr = s->it_dev;
+            bp.it = graph_it_off;
+        }
+        dim3 g((unsigned)(bp.n_marker + bp.rows_lb * s->tiles_x));
         // Programmatic dependent launch behind the previous iteration's lb_ib_tile_step: the
-        // kernel's fluid-independent prologue overlaps that kernel's tail.  Not right behind the
+        // marker CTAs' fluid-independent prologue overlaps that kernel's tail.  Not right behind the
         // kernels that write what the prologue reads (kinematics, tile lists), and not on tall
         // grids, where lb_fused_v2 of the previous iteration is the predecessor.
         cudaLaunchConfig_t cfg;

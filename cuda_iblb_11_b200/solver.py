@@ -11,13 +11,15 @@ import os
 import numpy as np
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libiblb.so")
+# IBLB_LIB: development only — another build of the same library (libiblb_checked.so)
+LIB_PATH = os.environ.get("IBLB_LIB") or os.path.join(_PKG, "libiblb.so")
 
 FLAG_HALF_FORCE_BODY = 1
 FLAG_PICK_HIGHEST_K = 2
 FLAG_NO_GRAPH = 4
 FLAG_NO_FUSE = 8
 FLAG_NO_PDL = 16
+FLAG_MUCUS = 32
 
 IPC_HANDLE_BYTES = 64
 
@@ -42,6 +44,8 @@ class Params(ctypes.Structure):
         ("gx", ctypes.c_double), ("gy", ctypes.c_double), ("u0_amp", ctypes.c_double),
         ("flags", ctypes.c_uint), ("device", ctypes.c_int),
         ("slab_x0", ctypes.c_uint), ("slab_w", ctypes.c_uint),
+        ("fine_points", ctypes.c_uint), ("shape_scale", ctypes.c_double),
+        ("flux_back", ctypes.c_uint),
     ]
 
     @classmethod
@@ -61,9 +65,15 @@ class Params(ctypes.Structure):
 
     @classmethod
     def channel(cls, XDIM, YDIM, c_num=0, c_space=48, c_fraction=1, Re=1.0, T_num=1.0, T_pow=5,
-                gx=0.0, gy=0.0, u0_amp=0.0, flags=0, device=-1, slab_x0=0, slab_w=0):
-        """Parameter block for an arbitrary channel (C2/C4 style) with the reference's scaling."""
+                gx=0.0, gy=0.0, u0_amp=0.0, flags=0, device=-1, slab_x0=0, slab_w=0,
+                LENGTH=0, fine_points=0, shape_scale=0.0, flux_back=0):
+        """Parameter block for an arbitrary channel (C2/C4 style) with the reference's scaling.
+        LENGTH / fine_points / shape_scale / flux_back: cilium geometry the reference hard-wires
+        (96 / 9600 / 111 / 5); 0 keeps its value."""
         p = cls.default()
+        if LENGTH:
+            p.LENGTH = LENGTH
+        p.fine_points, p.shape_scale, p.flux_back = fine_points, shape_scale, flux_back
         p.c_fraction, p.c_num, p.c_space = c_fraction, c_num, c_space
         p.Re, p.T_num, p.T_pow, p.I_pow, p.P_num = Re, T_num, T_pow, 1.0, 100
         p.XDIM, p.YDIM = XDIM, YDIM
@@ -97,7 +107,7 @@ SYMBOLS = [
     "iblb_set_fields", "iblb_marker_fine_index", "iblb_last_step_seconds",
     "iblb_last_step_launches", "iblb_profile_phases", "iblb_export_halo", "iblb_connect",
     "iblb_connect_local", "iblb_set_marker_replay", "iblb_run", "iblb_last_error", "iblb_version",
-    "iblb_save_checkpoint", "iblb_load_checkpoint",
+    "iblb_save_checkpoint", "iblb_load_checkpoint", "iblb_debug_violations",
 ]
 
 
@@ -141,6 +151,7 @@ def lib():
     L.iblb_connect_local.argtypes = [vp, vp, vp]
     L.iblb_set_marker_replay.argtypes = [vp, ctypes.c_uint, vp, ctypes.c_uint]
     L.iblb_run.argtypes = [ctypes.POINTER(Params), ctypes.c_char_p]
+    L.iblb_debug_violations.restype = ctypes.c_longlong
     _lib = L
     return L
 
@@ -159,7 +170,7 @@ class Solver:
         _check(lib().iblb_create(ctypes.byref(params), ctypes.byref(self._h)))
         self.width = params.slab_w if params.slab_w else params.XDIM
         self.size = self.width * params.YDIM
-        self.Ns = 96 * params.c_num
+        self.Ns = (params.LENGTH or 96) * params.c_num
 
     # --- stepping -------------------------------------------------------------------------
     def step(self, n=1):
@@ -273,6 +284,11 @@ class Solver:
             self.close()
         except Exception:
             pass
+
+
+def debug_violations():
+    """Index violations counted by an IBLB_CHECKED build of libiblb.so; -1 for a product build."""
+    return lib().iblb_debug_violations()
 
 
 def run(params, root=None):

@@ -46,6 +46,9 @@ extern "C" {
                                         fused IB+LB launch per iteration; same results bit for bit */
 #define IBLB_FLAG_NO_PDL 16u         /* no programmatic dependent launch between consecutive fused
                                         iterations (full kernel-to-kernel serialisation) */
+#define IBLB_FLAG_MUCUS 32u          /* the reference's other beat-shape coefficient set, "WITH
+                                        MUCUS PRESENT" (main.cu:36-54, commented out there); default:
+                                        the active "WITHOUT MUCUS" set (main.cu:56-74) */
 
 typedef struct iblb_params {
     /* --- the ten driver arguments, main.cu:291-296 --- */
@@ -68,6 +71,14 @@ typedef struct iblb_params {
     /* x-slab of a wider periodic channel (multi-GPU): this solver owns global columns
      * [slab_x0, slab_x0+slab_w); slab_w == 0 means the whole channel (single GPU). */
     unsigned slab_x0, slab_w;
+    /* cilium geometry the reference hard-wires; 0 = the reference's value.  LENGTH above is the
+     * number of markers per cilium (main.cu:83,180) as well as the length scale of TAU and of the
+     * output units (main.cu:279,312,320): 1..128. */
+    unsigned fine_points;  /* fine points per cilium that define_filament evaluates, main.cu:81
+                              (9600); marker j is the fine point k with |shape_scale*k/fine_points
+                              - j| < 0.01 (main.cu:158-172) — every marker must have one */
+    double shape_scale;    /* filament length scale in lattice units, main.cu:137-145 (111) */
+    unsigned flux_back;    /* the flux plane is x = XDIM - flux_back, ImmersedBoundary.cu:259 (5) */
 } iblb_params;
 
 typedef struct iblb_solver iblb_solver;
@@ -162,6 +173,10 @@ int iblb_load_checkpoint(iblb_solver *s, const char *path);
 /* Runs ITERATIONS steps writing the reference's Data/ tree under `root` (NULL: "Data/").
  * main.cu:589-631, 758-790, 936-1005, 1030-1060. */
 int iblb_run(const iblb_params *p, const char *root);
+
+/* Development: device-side index violations counted by a library built with IBLB_CHECKED=1
+ * (range checks on every population / band / marker / shared-table index); -1 in product builds. */
+long long iblb_debug_violations(void);
 
 const char *iblb_last_error(void);
 const char *iblb_version(void);

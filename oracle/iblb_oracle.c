@@ -54,12 +54,34 @@ static const double B_mn[7 * 2 * 3] = {
     -0.499, 0.423, 0.138,  0.125,  0.075,  0.067,  0.0,    -1.017, -0.276, -0.196, -0.037,
     0.025,  0.023, 0.0,    0.339,  -0.327, -0.114, -0.105, -0.057, -0.055};
 
-#define F_LENGTH 9600 /* main.cu:81 */
-#define LENGTH 96     /* main.cu:83 */
+/* main.cu:36-54 (coefficient set "WITH MUCUS PRESENT", commented out in the reference) */
+static const double A_mn_mucus[7 * 2 * 3] = {
+    -0.449, 0.130,  -0.169, 0.063,  -0.050, -0.040, -0.068, 2.076,  -0.003, 0.054,  0.007,
+    0.026,  0.022,  0.010,  -0.072, -1.502, 0.260,  -0.123, 0.011,  -0.009, 0.196,  -1.074,
+    -0.230, -0.305, -0.180, -0.069, 0.001,  -0.080, 0.658,  0.793,  -0.251, 0.049,  0.009,
+    0.023,  -0.111, 0.381,  0.331,  0.193,  0.082,  0.029,  0.002,  0.048};
+static const double B_mn_mucus[7 * 2 * 3] = {
+    0.0,   -0.030, -0.093, 0.037,  0.062,  0.016,  -0.065, 0.0,   0.080,  -0.044, -0.017,
+    0.052, 0.007,  0.051,  0.0,    1.285,  -0.036, -0.244, -0.093, -0.137, 0.095,  0.0,
+    -0.298, 0.513, 0.004,  -0.222, 0.035,  -0.128, 0.0,    -1.034, 0.050,  0.143,  0.043,
+    0.098, -0.054, 0.0,    0.210,  -0.367, 0.009,  0.120,  -0.024, 0.102};
+
+/* the reference's hard-wired geometry (ref_params fields of the same names override them) */
+#define F_LENGTH_REF 9600 /* main.cu:81 */
+#define LENGTH_REF 96     /* main.cu:83 */
+#define SCALE_REF 111.    /* main.cu:137-145 */
+#define FLUX_BACK_REF 5   /* ImmersedBoundary.cu:259 */
+/* run-time values */
+#define F_LENGTH (o->f_length)
+#define LENGTH (o->length)
+#define SCALE (o->scale)
 
 typedef struct Oracle {
     ref_params p;
     int size, Ns, it;
+    int length, f_length, flux_back; /* markers / fine points per cilium, flux plane offset */
+    double scale;                    /* 111 */
+    const double *A, *B;             /* beat-shape coefficient set */
     double *u, *rho, *f0, *f, *f1, *force, *F;
     float *s, *u_s, *F_s, *b_points;
     int *epsilon;
@@ -296,7 +318,7 @@ static void o_spread(Oracle *o, double gx, double gy) {
             o->rho[j];
     }
     /* the reference's order of the YDIM CAS-adds is arbitrary (Q10); ascending y here */
-    const int xq = XDIM - 5;
+    const int xq = XDIM - o->flux_back;
     for (int y = 0; y < YDIM; y++) o->Q += o->u[0 * size + y * XDIM + xq] / (double)YDIM;
 }
 
@@ -309,7 +331,7 @@ static void build_candidates(Oracle *o) {
     o->cand_j = (int *)malloc(sizeof(int) * cap);
     for (int k = 0; k < F_LENGTH; k++) {
         float arcl = 1. * k / F_LENGTH; /* :100 */
-        float s2 = 111 * arcl;          /* :139 */
+        float s2 = SCALE * arcl;        /* :139 */
         for (int j = 0; j < LENGTH; j++) {
             float b_length = j % LENGTH;
             if (fabsf(s2 - b_length) < 0.01) { /* :162 */
@@ -335,7 +357,7 @@ static void o_define_filament(Oracle *o, int it) {
     const int lowest = (o->p.flags & REF_FLAG_PICK_LOWEST_K) != 0;
 #pragma omp parallel for num_threads(o->threads)
     for (int m = 0; m < o->p.c_num; m++) {
-        char written[LENGTH];
+        char written[512];
         memset(written, 0, sizeof written);
         for (int q = 0; q < o->ncand; q++) {
             const int k = o->cand_k[q];
@@ -352,19 +374,19 @@ static void o_define_filament(Oracle *o, int it) {
                     a_n[2 * n + c] = 0.;
                     b_n[2 * n + c] = 0.;
                     for (int pw = 0; pw < 3; pw++) {
-                        a_n[2 * n + c] += A_mn[n + 14 * pw + 7 * c] * pow(arcl, pw + 1);
-                        b_n[2 * n + c] += B_mn[n + 14 * pw + 7 * c] * pow(arcl, pw + 1);
+                        a_n[2 * n + c] += o->A[n + 14 * pw + 7 * c] * pow(arcl, pw + 1);
+                        b_n[2 * n + c] += o->B[n + 14 * pw + 7 * c] * pow(arcl, pw + 1);
                     }
                 }
             }
-            s[0] = 1. * 111 * a_n[2 * 0 + 0] * 0.5 + offset; /* :137-139 */
-            s[1] = 1. * 111 * a_n[2 * 0 + 1] * 0.5;
-            s[2] = 111 * arcl;
+            s[0] = 1. * SCALE * a_n[2 * 0 + 0] * 0.5 + offset; /* :137-139 */
+            s[1] = 1. * SCALE * a_n[2 * 0 + 1] * 0.5;
+            s[2] = SCALE * arcl;
             for (int n = 1; n < 7; n++) { /* :141-145 */
-                s[0] += 1. * 111 *
+                s[0] += 1. * SCALE *
                         (a_n[2 * n + 0] * cos(n * 2. * PI_REF * phase / T) +
                          b_n[2 * n + 0] * sin(n * 2. * PI_REF * phase / T));
-                s[1] += 1. * 111 *
+                s[1] += 1. * SCALE *
                         (a_n[2 * n + 1] * cos(n * 2. * PI_REF * phase / T) +
                          b_n[2 * n + 1] * sin(n * 2. * PI_REF * phase / T));
             }
@@ -447,6 +469,16 @@ void *oracle_create(const ref_params *pp) {
     o->p = *pp;
     const ref_params *p = &o->p;
     const int size = o->size = p->XDIM * p->YDIM;
+    o->length = p->length > 0 ? p->length : LENGTH_REF;
+    o->f_length = p->fine_points > 0 ? p->fine_points : F_LENGTH_REF;
+    o->scale = p->shape_scale > 0. ? p->shape_scale : SCALE_REF;
+    o->flux_back = p->flux_back > 0 ? p->flux_back : FLUX_BACK_REF;
+    o->A = (p->flags & REF_FLAG_MUCUS) ? A_mn_mucus : A_mn;
+    o->B = (p->flags & REF_FLAG_MUCUS) ? B_mn_mucus : B_mn;
+    if (o->length > 512) {
+        free(o);
+        return NULL;
+    }
     o->Ns = LENGTH * p->c_num;
 #ifdef _OPENMP
     o->threads = p->threads > 0 ? p->threads : omp_get_max_threads();

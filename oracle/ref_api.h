@@ -31,6 +31,12 @@ typedef struct ref_params {
     double u0_amp;    /* initial u_x(y) = u0_amp*sin(2*pi*(y+0.5)/YDIM); 0 in the reference */
     int threads;      /* CPU builds: OpenMP threads (0 = all) */
     int flags;        /* must be 0 for the two reference builds; oracle port: REF_FLAG_* */
+    /* geometry the reference hard-wires (0 = its value); honoured by the oracle port only, the two
+     * reference builds require the defaults */
+    int length;         /* markers per cilium, main.cu:83,180,279 (96) */
+    int fine_points;    /* fine points per cilium, main.cu:81 (9600) */
+    double shape_scale; /* filament length scale, main.cu:137-145 (111) */
+    int flux_back;      /* flux plane x = XDIM - flux_back, ImmersedBoundary.cu:259 (5) */
 } ref_params;
 
 /* oracle-port extensions (documented deviations from the reference driver):
@@ -40,6 +46,10 @@ typedef struct ref_params {
  *   of the lower fine-point index instead of the higher one. */
 #define REF_FLAG_HALF_FORCE_BODY 1
 #define REF_FLAG_PICK_LOWEST_K 2
+/* MUCUS: the reference's other beat-shape coefficient set ("WITH MUCUS PRESENT", main.cu:36-54,
+ * commented out in the source); pinned against libiblb_ref_cpu_mucus.so, which is the reference
+ * compiled with that block swapped in (oracle/Makefile, ref_cpu_mucus). */
+#define REF_FLAG_MUCUS 4
 
 void *ref_create(const ref_params *p);
 int ref_step(void *h, int n_steps);

@@ -15,6 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 REF_FLAG_HALF_FORCE_BODY = 1
 REF_FLAG_PICK_LOWEST_K = 2
+REF_FLAG_MUCUS = 4  # oracle port; the reference side is libiblb_ref_cpu_mucus.so ("ref_cpu_mucus")
 
 
 class RefParams(ctypes.Structure):
@@ -24,6 +25,8 @@ class RefParams(ctypes.Structure):
         ("TAU", ctypes.c_double), ("TAU2", ctypes.c_double),
         ("gx", ctypes.c_double), ("gy", ctypes.c_double), ("u0_amp", ctypes.c_double),
         ("threads", ctypes.c_int), ("flags", ctypes.c_int),
+        ("length", ctypes.c_int), ("fine_points", ctypes.c_int),
+        ("shape_scale", ctypes.c_double), ("flux_back", ctypes.c_int),
     ]
 
 
@@ -41,6 +44,8 @@ _LIBS = {
     "oracle": ("oracle/libiblb_oracle.so", "oracle_"),
     "ref_cpu": ("oracle/_ref/libiblb_ref_cpu.so", "ref_"),
     "ref_cuda": ("oracle/_ref/libiblb_ref_cuda.so", "ref_"),
+    # the reference with its commented-out "WITH MUCUS PRESENT" coefficient block swapped in
+    "ref_cpu_mucus": ("oracle/_ref/libiblb_ref_cpu_mucus.so", "ref_"),
 }
 
 
@@ -52,21 +57,22 @@ def available(kind):
     return os.path.exists(lib_path(kind))
 
 
-def reference_tau(T=100000, Re=1.0):
+def reference_tau(T=100000, Re=1.0, LENGTH=96):
     """TAU, TAU2 of main.cu:314-321 (host C_S = 0.577, LENGTH = 96)."""
     speed = 0.8 * 1000 / T
-    tau = (speed * 96) / (Re * 0.577 * 0.577) + 1. / 2.
+    tau = (speed * LENGTH) / (Re * 0.577 * 0.577) + 1. / 2.
     tau2 = 1. / (12. * (tau - (1. / 2.))) + (1. / 2.)
     return tau, tau2
 
 
 def make_params(XDIM, YDIM=192, c_num=0, c_space=48, T=100000, c_fraction=1, Re=1.0,
-                gx=0.0, gy=0.0, u0_amp=0.0, threads=0, flags=0, TAU=None, TAU2=None):
-    tau, tau2 = reference_tau(T, Re)
+                gx=0.0, gy=0.0, u0_amp=0.0, threads=0, flags=0, TAU=None, TAU2=None,
+                length=0, fine_points=0, shape_scale=0.0, flux_back=0):
+    tau, tau2 = reference_tau(T, Re, length or 96)
     p_step = (T * c_fraction // c_num) if c_num else 0
     return RefParams(XDIM, YDIM, c_num, c_space, T, p_step,
                      tau if TAU is None else TAU, tau2 if TAU2 is None else TAU2,
-                     gx, gy, u0_amp, threads, flags)
+                     gx, gy, u0_amp, threads, flags, length, fine_points, shape_scale, flux_back)
 
 
 class Checker:
@@ -96,7 +102,7 @@ class Checker:
         if not self.h:
             raise RuntimeError("checker %s: create failed" % kind)
         self.size = params.XDIM * params.YDIM
-        self.Ns = 96 * params.c_num
+        self.Ns = (params.length or 96) * params.c_num
 
     def set_marker32_trace(self, trace):
         """oracle port only: trace[it, m] != 0 -> the higher fine point wins marker 32 at step it."""

@@ -23,10 +23,10 @@ import os
 import numpy as np
 import pytest
 
-from checkers import (REF_FLAG_HALF_FORCE_BODY, REF_FLAG_PICK_LOWEST_K, Checker, make_params,
-                      reference_tau, rel_l2)
-from cuda_iblb_11_b200 import (FLAG_HALF_FORCE_BODY, FLAG_NO_FUSE, FLAG_NO_GRAPH, FLAG_NO_PDL,
-                               FLAG_PICK_HIGHEST_K, Params, Solver)
+from checkers import (REF_FLAG_HALF_FORCE_BODY, REF_FLAG_MUCUS, REF_FLAG_PICK_LOWEST_K, Checker,
+                      make_params, reference_tau, rel_l2)
+from cuda_iblb_11_b200 import (FLAG_HALF_FORCE_BODY, FLAG_MUCUS, FLAG_NO_FUSE, FLAG_NO_GRAPH,
+                               FLAG_NO_PDL, FLAG_PICK_HIGHEST_K, Params, Solver)
 
 pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
@@ -397,6 +397,55 @@ def test_marker_replay_off_restores_computed_kinematics():
     assert np.array_equal(a.markers()[0], c.markers()[0])
     for s in (a, b, c):
         s.close()
+
+
+# ------------------------------------------------------------------------------ generalised geometry
+@pytest.mark.parametrize("geo,X,Y,c_num,c_space", [
+    (dict(), 288, 192, 6, 48),                                                  # mucus table only
+    (dict(LENGTH=64, fine_points=6400, shape_scale=74.0, flux_back=9), 256, 128, 4, 64),
+    (dict(LENGTH=128, fine_points=12800, shape_scale=148.0, flux_back=1), 512, 256, 4, 128),
+    (dict(LENGTH=96, fine_points=9600, shape_scale=111.0, flux_back=5), 288, 192, 6, 48),
+])
+@pytest.mark.parametrize("mucus", [False, True])
+def test_generalised_cilium_geometry_matches_oracle(geo, X, Y, c_num, c_space, mucus):
+    """markers per cilium (LENGTH, main.cu:83,180,279), fine points (main.cu:81), the
+    filament scale (111, main.cu:137-145), the flux plane (XDIM-5, ImmersedBoundary.cu:259) and the
+    beat-shape coefficient set ("WITH MUCUS PRESENT", main.cu:36-54, via IBLB_FLAG_MUCUS) are
+    run-time parameters with the reference's values as defaults; the force band follows the cilia's
+    reach.  Fused and unfused paths bit-identical; both against the oracle, whose mucus table is
+    pinned to the reference built with that block swapped in (tests/test_oracle_pin.py)."""
+    kw = dict(c_num=c_num, c_space=c_space, c_fraction=c_num, **geo)
+    fl = FLAG_MUCUS if mucus else 0
+    a = Solver(Params.channel(X, Y, flags=fl, **kw))
+    b = Solver(Params.channel(X, Y, flags=fl | FLAG_NO_FUSE | FLAG_NO_GRAPH, **kw))
+    o = Checker("oracle", make_params(
+        X, Y, c_num=c_num, c_space=c_space, c_fraction=c_num, threads=8,
+        flags=REF_FLAG_PICK_LOWEST_K | (REF_FLAG_MUCUS if mucus else 0),
+        length=geo.get("LENGTH", 0), fine_points=geo.get("fine_points", 0),
+        shape_scale=geo.get("shape_scale", 0.0), flux_back=geo.get("flux_back", 0)))
+    assert a.Ns == o.Ns
+    for n in (1, 4, 35):
+        a.step(n)
+        b.step(n)
+        o.step(n)
+        for x, y in zip(a.fields() + a.markers() + (a.force(),), b.fields() + b.markers() + (b.force(),)):
+            assert np.array_equal(x, y)
+        assert a.Q == b.Q
+        compare_ib(a, o, "it=%d" % a.it)
+    assert a.Q != 0.0
+    for s in (a, b):
+        s.close()
+    o.close()
+
+
+def test_geometry_without_a_fine_point_for_every_marker_is_refused():
+    """main.cu:158-172 picks marker j from the fine points with |scale*k/fine - j| < 0.01; a
+    combination that leaves a marker without any would keep it at the origin for ever."""
+    with pytest.raises(Exception, match="no fine point"):
+        Solver(Params.channel(288, 192, c_num=6, LENGTH=96, fine_points=100, shape_scale=111.0))
+    with pytest.raises(Exception, match="YDIM must be at least"):
+        Solver(Params.channel(512, 128, c_num=4, c_space=128, LENGTH=128, fine_points=12800,
+                              shape_scale=148.0))
 
 
 # ------------------------------------------------------------------------------ execution modes

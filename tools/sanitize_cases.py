@@ -1,8 +1,13 @@
 #!/usr/bin/env python
-"""Small runs of every launch mode, meant to be executed under compute-sanitizer (GPU box):
+"""Small runs of every launch mode against the range-checked build of the library (GPU box):
 
-    compute-sanitizer --tool memcheck  python tools/sanitize_cases.py c1_fused
-    compute-sanitizer --tool racecheck python tools/sanitize_cases.py split1024
+    python -m cuda_iblb_11_b200.build --checked
+    IBLB_LIB=cuda_iblb_11_b200/libiblb_checked.so python tools/sanitize_cases.py c1_fused split1024 ...
+
+(compute-sanitizer, for which these cases were written, is closed on the GPU pool:
+profiles/r02_sanitizer_unavailable.md.)  The checked build counts, on the device, every index into
+the population buffers, force band, marker arrays and shared-memory tables that leaves its range;
+each case prints that count, which must be 0.
 
 Cases: c1_fused (CUDA graph + programmatic dependent launch, 70 iterations), c1_nofuse (separate
 kinematics / interpolate / spread / LB kernels), split1024 (tall grid: band tiles + lb_fused_v2 above),
@@ -18,7 +23,8 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from cuda_iblb_11_b200 import FLAG_NO_FUSE, FLAG_NO_GRAPH, Params, Solver, slabs  # noqa: E402
+from cuda_iblb_11_b200 import (FLAG_NO_FUSE, FLAG_NO_GRAPH, Params, Solver, debug_violations,  # noqa: E402
+                               slabs)
 
 
 def same(a, b):
@@ -94,4 +100,7 @@ def getters():
 if __name__ == "__main__":
     for name in sys.argv[1:]:
         globals()[name]()
-        print("case %s ok" % name, flush=True)
+        v = debug_violations()
+        print("case %s ok, index violations so far: %s" % (
+            name, "n/a (product build)" if v < 0 else v), flush=True)
+        assert v <= 0, "range check failed"
