@@ -9,6 +9,8 @@
 //   IBLB_DEVICE CUDA device (default 0; the reference uses 3 when ShARC=1, main.cu:395-396)
 //   IBLB_YDIM   channel height (default 192)        IBLB_GX  uniform body force
 //   IBLB_ITERATIONS  override the iteration count (smoke runs)
+//   IBLB_GPUS   x-slabs over that many GPUs of this machine (default 1), first device IBLB_DEVICE
+//   IBLB_CHECKPOINT / IBLB_RESTART   checkpoint file written at every output interval / read at start
 #include <cstdlib>
 #include <iostream>
 

@@ -3,31 +3,33 @@
 //   every kKinBatch iterations   ib_kinematics_batch   markers: kinematics, epsilon, stencils  (ib_kernels.cu)
 //                                ib_tile_lists         per band tile and iteration: the ascending list of
 //                                                      markers whose 3x3 support can touch the tile
-//   every iteration              lb_ib_tile_step       marker CTAs: F_s of a tile's markers -> the tile's force
-//                                                      LB CTAs: pull-stream, moments, TRT collide + Guo
+//   every iteration              lb_ib_tile_step       F_s of the tile's markers -> spread -> pull-stream,
+//                                 (or lb_ib_roles_step) moments, TRT collide + Guo
 //
 // Replaces the reference's interpolate, spread, streaming, macro, equilibrium, collision launches
 // (ImmersedBoundary.cu:94-267, LatticeBoltzmann.cu:30-411).  A tile is 8 (or 6) columns x 64 rows
 // (warp = column, lane = row pair).  Everything about the markers that does not depend on the fluid
 // — positions, velocities, epsilon, delta factors AND which markers reach which tile — is prescribed
 // (main.cu:77-252 is a function of `it` alone) and is computed off the fluid's critical path for a
-// batch of iterations.  What is left per iteration is split between two kinds of CTA of ONE grid:
+// batch of iterations.  What is left per iteration comes in two forms, same device functions, same
+// bits (tests/test_gpu_parity.py), chosen per grid by iblb_create:
 //
-//   * marker CTAs (the lowest block indices, one per band tile that has markers): rho, u* of the
-//     support nodes straight from the post-collision populations (nine pulled populations each,
-//     ImmersedBoundary.cu:94-133), F_s of the markers on the tile's list (a marker that reaches two
-//     tiles is evaluated by both: no dependency between marker CTAs), every node of the tile sums
-//     its spreading terms in ascending marker order (ImmersedBoundary.cu:178-203), the tile's force
-//     goes to the band buffer and the tile's flag is released with the iteration number;
-//   * LB CTAs (every tile): issue their population loads, and — band tiles with markers only —
-//     acquire the tile's flag while those loads are in flight, read the two force values per node
-//     pair, collide, store.  They hold no shared memory and lb_fused_v2's registers.
+// lb_ib_tile_step (grids of about one wave of CTAs: the reference's own scripts): the tile's CTA does
+//   everything.  It forms rho, u* of the support nodes it holds from the populations it pulls anyway
+//   and pulls those of the two rings around it, evaluates F_s of every marker on its list (nine
+//   support nodes each, ImmersedBoundary.cu:94-133; a marker that reaches two tiles is evaluated by
+//   both: no inter-CTA dependency, no atomics), then every node sums its spreading terms in
+//   ascending marker order (ImmersedBoundary.cu:178-203).  Neither F_s nor the force goes through
+//   global memory.  128 registers + 75 KB of shared memory: two CTAs per SM.
 //
-// The marker chain (scattered pulls -> moments -> F_s -> spreading) therefore runs BESIDE the LB
-// tile's own load phase instead of in front of its collision, and the tiles without markers are as
-// light as the pure-LB kernel.  Lower block indices are dispatched first, so an LB CTA never waits
-// for a marker CTA that is not resident; the spin is bounded all the same.  Same device functions
-// as lb_fused_v2 / ib_interp / ib_spread: bit-identical results (tests/test_gpu_parity.py).
+// lb_ib_roles_step (grids of several waves): two kinds of CTA in ONE grid.  Marker CTAs (the lowest
+//   block indices, one per band tile with markers) pull the support nodes, evaluate F_s, spread, store
+//   the tile's force in the band buffer and release the tile's flag with the iteration number; LB
+//   CTAs (every tile; lb_fused_v2's footprint, three per SM) issue their population loads, acquire
+//   the flag while those are in flight, read two force values per node pair, collide, store.  Lower
+//   block indices are dispatched first, so an LB CTA never waits for a marker CTA that is not
+//   resident; the spin is bounded all the same.  On one wave the extra L2 round trips (fence, flag,
+//   force) make it slower than the single-CTA form (profiles/r02_time_small_role_split.log).
 #include "ib_device.cuh"
 #include "iblb_device.cuh"
 #include "lb_device.cuh"
@@ -71,6 +73,26 @@ __device__ __forceinline__ int cta_rank(bool take, int *wcount, int &total) {
     return r;
 }
 
+// moment-table cell of ring node idx in [0, 4*kTabY + 4*tw) of a tile tw columns wide
+__device__ __forceinline__ int ring_cell(int idx, int tw) {
+    int lx, ly;
+    if (idx < 2 * kTabY) {  // two columns left of the tile
+        lx = idx / kTabY;
+        ly = idx - lx * kTabY;
+    } else if (idx < 4 * kTabY) {  // two columns right of it
+        const int r = idx - 2 * kTabY;
+        lx = r / kTabY;
+        ly = r - lx * kTabY;
+        lx += tw + 2;
+    } else {  // two rows below, two above
+        const int r = idx - 4 * kTabY;
+        const int row = r / tw;
+        lx = 2 + (r - row * tw);
+        ly = row < 2 ? row : 64 + row;
+    }
+    return lx * kTabY + ly;
+}
+
 // rho, u* of table cell c (a ring node, or an own node of a column past the channel), pulled from
 // global memory as the reference's interpolate would address it
 __device__ __forceinline__ void tile_pulled_cell(const Lattice &L, const double *__restrict__ src,
@@ -82,6 +104,15 @@ __device__ __forceinline__ void tile_pulled_cell(const Lattice &L, const double 
     sh.rho[c] = rho;
     sh.ux[c] = ux;
     sh.uy[c] = uy;
+}
+
+// rho and u* = sum c f / rho of pulled populations, same order as support_node_moments
+__device__ __forceinline__ void node_moments(const double (&f)[9], double &rho, double &ux,
+                                             double &uy) {
+    const double r = DA(DA(DA(DA(DA(DA(DA(DA(f[0], f[1]), f[2]), f[3]), f[4]), f[5]), f[6]), f[7]), f[8]);
+    rho = r;
+    ux = __ddiv_rn(DA(DS(DS(DA(DS(f[1], f[3]), f[5]), f[6]), f[7]), f[8]), r);
+    uy = __ddiv_rn(DS(DS(DA(DA(DS(f[2], f[4]), f[5]), f[6]), f[7]), f[8]), r);
 }
 
 // table cell of the centre of a marker's 3x3 support (ImmersedBoundary.cu:108-109: nearbyint of the
@@ -318,6 +349,7 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
         if (t == 0) {
             atomicExch(p.err, 1);
             pg.n = 0;
+            pg.nring = 0;
             pg.ncell = 0;
         }
         return;
@@ -364,7 +396,21 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
 #pragma unroll
     for (int w = 0; w < kHitWords; w++)
         pg.hit[w][t] = w * 32 < n ? hit_mask32(sbase, w * 32, n, tx0 + warp, ty0 + 2 * lane) : 0u;
-    // the support nodes (in the tile or in the two rings around it), as cells of the moment table
+    {
+        const int c = (warp + 2) * kTabY + 2 * lane + 2;
+        pg.own[t] = (unsigned char)((need[c] ? 1 : 0) | (need[c + 1] ? 2 : 0));
+    }
+    int nring = 0;
+    const int nring_all = 4 * kTabY + 4 * tw;
+    for (int i0 = 0; i0 < nring_all; i0 += 256) {
+        const int idx = i0 + t;
+        const bool take = idx < nring_all && need[ring_cell(idx, tw)] != 0;
+        int total;
+        const int r = nring + cta_rank(take, wcount, total);
+        if (take) pg.ring[r] = (short)idx;
+        nring += total;
+    }
+    // the same support nodes, in the tile or around it, as cells of the moment table (role-split kernel)
     int ncell = 0;
     for (int i0 = 0; i0 < kTabCells; i0 += 256) {
         const int idx = i0 + t;
@@ -377,6 +423,7 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
     }
     if (t == 0) {
         pg.n = n;
+        pg.nring = nring;
         pg.ncell = ncell;
     }
 }
@@ -510,7 +557,7 @@ __device__ __forceinline__ void lb_cta(const BandParams &p, int b) {
 // grid = n_marker + rows_lb * tiles_x CTAs of 32*tw threads.  Requires YDIM % 64 == 0 and a solver
 // that owns the whole channel (ghost columns = its own opposite edge).  On tall grids rows_lb covers
 // the band only and lb_fused_v2 takes the rows above.  p.M and p.prog point at the iteration's slot.
-__global__ void __launch_bounds__(256, 3) lb_ib_tile_step(const BandParams p) {
+__global__ void __launch_bounds__(256, 3) lb_ib_roles_step(const BandParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];  // marker CTAs only
     // Programmatic dependent launch: the next iteration's CTAs may start as soon as every CTA of
     // this one is running; each role calls pdl_wait() before it touches the populations.
@@ -520,10 +567,148 @@ __global__ void __launch_bounds__(256, 3) lb_ib_tile_step(const BandParams p) {
     else lb_cta(p, b - p.n_marker);
 }
 
+// grid = (row tiles, ceil(W/8)), block = 256.  Requires YDIM % 64 == 0 and a solver that owns the
+// whole channel (ghost columns = its own opposite edge).  Row tiles >= band_rows/64 are plain LB;
+// on tall grids only the band tiles are launched here and lb_fused_v2 takes the rows above.
+// p.M and p.prog point at the iteration's slot.
+__global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];  // kTileSmemBytes, dynamic
+    TileMarkers &sh = *reinterpret_cast<TileMarkers *>(smem_raw);
+    SpreadLists &sl = *reinterpret_cast<SpreadLists *>(smem_raw + sizeof(TileMarkers));
+    const LbParams &lp = p.lb;
+    const Lattice &L = lp.L;
+    const int tile_y = blockIdx.x, tile_x = blockIdx.y;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int tw = p.tw, NT = tw * 32;  // columns per tile = warps of this CTA; threads
+    const int tx0 = tile_x * tw, ty0 = tile_y * 64;
+    const int x = tx0 + warp;
+    const int y0 = ty0 + 2 * lane;
+    const bool active = x < L.W;  // warp-uniform
+    const bool band_tile = ty0 < p.band_rows;  // block-uniform
+
+    // Programmatic dependent launch: the next iteration's CTAs may start as soon as every CTA of
+    // this one is running.  Everything up to pdl_wait() reads only the prescribed marker data (the
+    // tile's plan and its markers, written by kernels that completed before the first kernel of this
+    // PDL chain started), so it overlaps the tail of the previous iteration; pdl_wait() returns once
+    // the previous iteration has completed and its populations are visible.
+    pdl_launch_dependents();
+    int n = 0, nring = 0;
+    const TileProgram *__restrict__ pg = nullptr;
+    if (band_tile) {
+        pg = p.prog + ((long long)tile_y * p.tiles_x + tile_x);
+        n = __ldg(&pg->n);
+        nring = __ldg(&pg->nring);
+    }
+    int r0 = 0, r1 = 0, own = 0;
+    unsigned hit[kHitWords] = {0u, 0u, 0u, 0u};
+    if (n > 0) {  // block-uniform
+        int k0 = 0, k1 = 0;
+        if (t < n) k0 = __ldg(pg->list + t);
+        if (t + NT < n) k1 = __ldg(pg->list + t + NT);
+        if (t < nring) r0 = __ldg(pg->ring + t);
+        if (t + NT < nring) r1 = __ldg(pg->ring + t + NT);
+        own = __ldg(pg->own + t);
+#pragma unroll
+        for (int w = 0; w < kHitWords; w++)
+            if (w * 32 < n) hit[w] = __ldg(&pg->hit[w][t]);
+#pragma unroll
+        for (int r = 0; r < 2; r++) {
+            const int e = t + NT * r;
+            if (e < n) {
+                const int k = r ? k1 : k0;
+                const float2 sm = p.M.s[k], us = p.M.u_s[k];
+                const int2 b = p.M.base[k];
+                sh.su[e] = make_float4(sm.x, sm.y, us.x, us.y);
+                sh.fb[e] = make_float4(0.f, 0.f, __int_as_float(b.x), __int_as_float(b.y));
+                sh.wx[e] = p.M.wx[k];
+                sh.wy[e] = p.M.wy[k];
+            }
+        }
+    }
+    int nlist = 0;
+    if (n > 0) {
+        __syncthreads();  // the staged markers
+        nlist = build_spread_list(sh, sl, n, x + L.x0, y0, hit);
+    }
+    pdl_wait();
+    Pulled q;
+    if (active) load_pulled(L, lp.src, x, y0, lane, q);
+
+    // the support nodes in the two rings around the tile: the first 256 are pulled into registers
+    // now and turned into moments after this thread's own nodes, so that their latency overlaps
+    double rf[9] = {1., 0., 0., 0., 0., 0., 0., 0., 0.};
+    bool rvalid = false;
+    int rc0 = 0;
+    if (t < nring) {
+        rc0 = ring_cell(r0, tw);
+        const int lx = rc0 / kTabY, ly = rc0 - lx * kTabY;
+        rvalid = support_node_pull(L, lp.src, tx0 + L.x0 - 2 + lx, ty0 - 2 + ly, rf);
+    }
+    if (n > 0) {
+        if (t + NT < nring) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, ring_cell(r1, tw));
+        if (!active) {  // columns past the channel (W % 8 != 0): as the reference would address them
+            const int c = (warp + 2) * kTabY + 2 * lane + 2;
+            if (own & 1) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, c);
+            if (own & 2) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, c + 1);
+        }
+    }
+
+    double a[9], b[9];
+    if (active) shift_pulled(q, lane, a, b);
+
+    double Fx0 = lp.gx, Fy0 = lp.gy, Fx1 = lp.gx, Fy1 = lp.gy;
+    bool forced = (lp.gx != 0.0) | (lp.gy != 0.0);
+    if (band_tile) forced = true;  // as the reference: spread's velocity update covers every node
+    if (n > 0) {
+        if (active) {  // this thread's support nodes: moments of the populations it pulled anyway
+            const int c = (warp + 2) * kTabY + 2 * lane + 2;
+            // a warp with any support node forms both nodes' moments in every lane, without
+            // branches (the two divisions per node overlap); cells nobody needs are never read
+            if (__any_sync(0xffffffffu, own != 0)) {
+                double r0_, x0_, y0_, r1_, x1_, y1_;
+                node_moments(a, r0_, x0_, y0_);
+                node_moments(b, r1_, x1_, y1_);
+                sh.rho[c] = r0_; sh.ux[c] = x0_; sh.uy[c] = y0_;
+                sh.rho[c + 1] = r1_; sh.ux[c + 1] = x1_; sh.uy[c + 1] = y1_;
+            }
+        }
+        if (t < nring) {
+            double rho, ux, uy;
+            node_moments(rf, rho, ux, uy);  // rf = (1, 0, ...) placeholder when !rvalid
+            sh.rho[rc0] = rvalid ? rho : 0.;
+            sh.ux[rc0] = rvalid ? ux : 0.;
+            sh.uy[rc0] = rvalid ? uy : 0.;
+        }
+        __syncthreads();
+        if (t < n) tile_marker_force(sh, tx0 + L.x0, ty0, tw, t);
+        if (t + NT < n) tile_marker_force(sh, tx0 + L.x0, ty0, tw, t + NT);
+        __syncthreads();
+        double fx0 = 0., fy0 = 0., fx1 = 0., fy1 = 0.;
+        list_spread(sh, sl, nlist, fx0, fy0, fx1, fy1);
+        tile_spread(sh, n, x + L.x0, y0, hit, fx0, fy0, fx1, fy1);  // what did not fit the list
+        Fx0 += fx0; Fy0 += fy0; Fx1 += fx1; Fy1 += fy1;
+    }
+    if (!active) return;
+    const double ux0 = collide_node(a, Fx0, Fy0, forced, lp);
+    const double ux1 = collide_node(b, Fx1, Fy1, forced, lp);
+    store_pair(lp, x, y0, a, b);
+
+    // flux through x = XDIM-5 (ImmersedBoundary.cu:259-264), same slots and order as lb_fused_v2
+    if (x == lp.xq && lp.qacc != nullptr) {
+        double s = ux0 + ux1;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+        if (lane == 0) lp.qacc[tile_y] += s / (double)L.YDIM;
+    }
+}
+
 // dynamic shared memory of lb_ib_tile_step (above the 48 KB static limit: opt-in per device)
 size_t tile_step_smem_bytes() { return sizeof(TileMarkers) + sizeof(SpreadLists); }
 cudaError_t tile_step_prepare() {
-    return cudaFuncSetAttribute(lb_ib_tile_step, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(lb_ib_tile_step, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)tile_step_smem_bytes());
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(lb_ib_roles_step, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)tile_step_smem_bytes());
 }
 

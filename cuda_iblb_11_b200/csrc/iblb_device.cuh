@@ -89,7 +89,8 @@ struct LbParams {
     // columns this launch covers: c in [0, col_count) -> x = col_begin + c, and x += split_skip
     // when x >= split_at (boundary launch = the first and last G columns in one grid)
     int col_begin, col_count, split_at, split_skip;
-    int row_begin;  // first row this launch covers (multiple of 64; lb_fused_v2 only)
+    int row_begin;  // rows [row_begin, row_end) this launch covers (multiples of 64, of 128 for
+    int row_end;    // lb_fused_v4; vector kernels only); row_end == 0 means YDIM
 };
 
 struct MarkerArrays {
@@ -132,13 +133,17 @@ constexpr int kTabCells = kTabX * kTabY;
 
 // Everything about one band tile at one iteration that does not depend on the fluid (the cilia are
 // prescribed), written by ib_tile_lists for a batch of iterations, read by lb_ib_tile_step.
+constexpr int kRingNodes = 304;   // nodes of the two rings around an 8x64 tile (the widest)
 struct TileProgram {
     int n;                        // markers (epsilon != 0) whose 3x3 support can touch the tile
-    int ncell;                    // nodes in and around the tile that are support nodes of these
-    int pad[2];
+    int nring;                    // ring nodes that are support nodes of these markers
+    int ncell;                    // all support nodes, in the tile and in the rings
+    int pad;
     int list[kTileCap];           // the markers' indices, ascending (the reference's summation order)
     unsigned hit[kHitWords][256]; // per thread (node pair): which of list[32w..32w+31] force its nodes
-    short cells[kTabCells];       // the support nodes, as cells of the tile's moment table
+    short ring[kRingNodes];       // lb_ib_tile_step: the needed ring nodes ...
+    unsigned char own[256];       // ... and per thread: bit 0/1 = node y0 / y0+1 is a support node
+    short cells[kTabCells];       // lb_ib_roles_step: all support nodes as cells of the moment table
 };
 static_assert(sizeof(TileProgram) % 16 == 0, "TileProgram alignment");
 
@@ -151,8 +156,8 @@ struct BandParams {
     int tiles_x;             // column tiles = ceil(W/tw)
     TileProgram *prog;       // [slot][band row tile][column tile]
     int *err;                // set non-zero when a tile exceeds kBandMaxRel / kTileCap
-    // lb_ib_tile_step: the first n_marker CTAs evaluate the markers of one band tile each and leave
-    // the tile's force in the band buffer; the others are the LB tiles
+    // lb_ib_roles_step only: the first n_marker CTAs evaluate the markers of one band tile each and
+    // leave the tile's force in the band buffer; the others are the LB tiles
     double *band_w;          // the force band, written by the marker CTAs (lb.band reads it)
     int *tile_flag;          // per band tile: (iteration + 1) whose force the band holds
     const int *it_ptr;       // iteration = (it_ptr ? *it_ptr : 0) + it

@@ -20,6 +20,7 @@ int cuda_fail(cudaError_t e, const char *what);
 
 // kernels (lb_kernels.cu / ib_kernels.cu)
 __global__ void lb_fused_v2(const LbParams p);
+__global__ void lb_fused_v4(const LbParams p);
 __global__ void lb_fused_v1(const LbParams p, double *qpart);
 __global__ void flux_reduce_v1(const double *qpart, int n, double *qacc);
 __global__ void lb_init(const LbParams p, const double *rho_in, const double *u_in, double u0_amp,
@@ -33,6 +34,7 @@ __global__ void ib_interp(const IbParams p);
 __global__ void ib_spread(const IbParams p);
 __global__ void ib_tile_lists(const BandParams p);
 __global__ void lb_ib_tile_step(const BandParams p);
+__global__ void lb_ib_roles_step(const BandParams p);
 __global__ void it_advance(int *it_ptr, int by);
 unsigned long long checked_count_lb();     // IBLB_CHECKED builds: index violations per
 unsigned long long checked_count_ib();     // translation unit (0 in product builds)
@@ -52,6 +54,7 @@ struct iblb_solver {
     iblb::Lattice L;
     int device;
     bool vec2;                 // fast path usable (YDIM % 64 == 0)
+    bool vec4;                 // lb_fused_v4 (256-bit accesses) where a launch's rows allow it
     double *buf[2];            // population buffers A/B
     int cur;                   // buffer the NEXT step pulls from
     unsigned it;               // completed iterations
@@ -72,6 +75,7 @@ struct iblb_solver {
     bool ib_stale;             // F_s / force band not materialised for the last step
     bool pdl_chain;            // the last kernel enqueued was lb_ib_tile_step over the whole grid
     iblb::TileProgram *prog;   // per slot and band tile: fluid-independent plan (ib_tile_lists)
+    bool roles;                // lb_ib_roles_step (marker CTAs + LB CTAs) instead of lb_ib_tile_step
     int tile_w;                // columns per tile of lb_ib_tile_step: 8, or 6 where that fills the SMs better
     int tiles_x, band_tiles;   // column tiles, band row tiles
     int *tile_flag;            // per band tile: iteration + 1 whose force the band buffer holds

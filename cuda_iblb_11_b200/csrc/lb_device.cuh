@@ -199,5 +199,116 @@ __device__ __forceinline__ void store_pair(const LbParams &p, int x, int y0, con
     }
 }
 
+// ---- four vertically adjacent nodes per thread (lb_fused_v4): 256-bit loads and stores ----------
+struct __align__(32) double4v {
+    double x, y, z, w;
+};
+__device__ __forceinline__ double4v ldg4(const double *p) {  // LDG.E.256, read-only path
+    double4v v;
+    asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];"
+                 : "=d"(v.x), "=d"(v.y), "=d"(v.z), "=d"(v.w)
+                 : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void stg4(double *p, double a, double b, double c, double d) {
+    asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d)
+                 : "memory");
+}
+
+// The nine populations the nodes (y0 .. y0+3) of column x pull, as loaded: one aligned 256-bit load
+// per population from the column it streams from, plus the row below lane 0 / above lane 31
+// (walls folded in exactly as in Pulled / load_pulled).
+struct Pulled4 {
+    double4v v[9];
+    double e2, e5, e6, e4, e7, e8;
+    bool bot, top;
+};
+
+__device__ __forceinline__ void load_pulled4(const Lattice &L, const double *__restrict__ src, int x,
+                                             int y0, int lane, Pulled4 &q) {
+    const long long P = L.plane;
+    const long long cm = L.off(x - 1, y0), c0 = L.off(x, y0), cp = L.off(x + 1, y0);
+    q.bot = (y0 == 0);
+    q.top = (y0 + 4 == L.YDIM);
+    q.v[0] = ldg4(src + 0 * P + c0);
+    q.v[1] = ldg4(src + 1 * P + cm);
+    q.v[2] = ldg4(src + 2 * P + c0);
+    q.v[3] = ldg4(src + 3 * P + cp);
+    q.v[4] = ldg4(src + 4 * P + c0);
+    q.v[5] = ldg4(src + 5 * P + cm);
+    q.v[6] = ldg4(src + 6 * P + cp);
+    q.v[7] = ldg4(src + 7 * P + cp);
+    q.v[8] = ldg4(src + 8 * P + cm);
+    q.e2 = q.e5 = q.e6 = q.e4 = q.e7 = q.e8 = 0.;
+    if (lane == 0) {
+        if (q.bot) {
+            q.e5 = __ldg(src + 7 * P + c0);
+            q.e6 = __ldg(src + 8 * P + c0);
+        } else {
+            q.e2 = __ldg(src + 2 * P + c0 - 1);
+            q.e5 = __ldg(src + 5 * P + cm - 1);
+            q.e6 = __ldg(src + 6 * P + cp - 1);
+        }
+    }
+    if (lane == 31) {
+        if (q.top) {
+            q.e7 = __ldg(src + 6 * P + c0 + 3);
+            q.e8 = __ldg(src + 5 * P + c0 + 3);
+        } else {
+            q.e4 = __ldg(src + 4 * P + c0 + 4);
+            q.e7 = __ldg(src + 7 * P + cp + 4);
+            q.e8 = __ldg(src + 8 * P + cm + 4);
+        }
+    }
+}
+
+// n0..n3 = nodes y0..y0+3: the six populations with c_y != 0 shifted by one row in registers
+__device__ __forceinline__ void shift_pulled4(const Pulled4 &q, int lane, double (&n0)[9],
+                                              double (&n1)[9], double (&n2)[9], double (&n3)[9]) {
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+        if (i == 0 || i == 1 || i == 3) {
+            n0[i] = q.v[i].x; n1[i] = q.v[i].y; n2[i] = q.v[i].z; n3[i] = q.v[i].w;
+        } else if (i == 2 || i == 5 || i == 6) {  // c_y = +1: from the row below
+            const double t = shfl_up1(q.v[i].w);
+            const double e = i == 2 ? (q.bot ? q.v[4].x : q.e2) : i == 5 ? q.e5 : q.e6;
+            n0[i] = lane == 0 ? e : t;
+            n1[i] = q.v[i].x; n2[i] = q.v[i].y; n3[i] = q.v[i].z;
+        } else {  // c_y = -1: from the row above
+            const double t = shfl_dn1(q.v[i].x);
+            const double e = i == 4 ? (q.top ? q.v[2].w : q.e4) : i == 7 ? q.e7 : q.e8;
+            n0[i] = q.v[i].y; n1[i] = q.v[i].z; n2[i] = q.v[i].w;
+            n3[i] = lane == 31 ? e : t;
+        }
+    }
+}
+
+__device__ __forceinline__ void store_quad(const LbParams &p, int x, int y0, const double (&n0)[9],
+                                           const double (&n1)[9], const double (&n2)[9],
+                                           const double (&n3)[9]) {
+    const Lattice &L = p.L;
+    const long long c0 = L.off(x, y0);
+#pragma unroll
+    for (int i = 0; i < 9; i++) stg4(p.dst + i * L.plane + c0, n0[i], n1[i], n2[i], n3[i]);
+    if (x < p.left.G) {  // see store_pair: three crossing populations when G == 1
+        const Remote &r = p.left;
+        const bool all = r.G > 1;
+#pragma unroll
+        for (int i = 0; i < 9; i++)
+            if (all || i == 3 || i == 6 || i == 7)
+                stg4(r.base + (long long)i * r.plane + (long long)(r.W + x + r.G) * r.ld + y0, n0[i],
+                     n1[i], n2[i], n3[i]);
+    }
+    if (x >= L.W - p.right.G) {
+        const Remote &r = p.right;
+        const bool all = r.G > 1;
+#pragma unroll
+        for (int i = 0; i < 9; i++)
+            if (all || i == 1 || i == 5 || i == 8)
+                stg4(r.base + (long long)i * r.plane + (long long)(x - L.W + r.G) * r.ld + y0, n0[i],
+                     n1[i], n2[i], n3[i]);
+    }
+}
+
 }  // namespace
 }  // namespace iblb

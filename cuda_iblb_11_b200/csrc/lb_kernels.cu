@@ -25,7 +25,7 @@ namespace iblb {
 // Fast path: YDIM % 64 == 0.  grid = ceil(W*YDIM/2 / 256), block = 256.
 __global__ void __launch_bounds__(256, 3) lb_fused_v2(const LbParams p) {
     const Lattice &L = p.L;
-    const int HP = (L.YDIM - p.row_begin) >> 1;  // row pairs per column (multiple of 32)
+    const int HP = ((p.row_end ? p.row_end : L.YDIM) - p.row_begin) >> 1;  // row pairs per column (multiple of 32)
     const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (gid >= (long long)p.col_count * HP) return;  // whole warps only
     const int c = (int)(gid / HP);
@@ -62,6 +62,48 @@ __global__ void __launch_bounds__(256, 3) lb_fused_v2(const LbParams p) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
         if (lane == 0) p.qacc[y0 >> 6] += s / (double)L.YDIM;
+    }
+}
+
+// Four nodes per thread, 256-bit loads and stores (LDG.E.256 / STG.E.256): rows [row_begin, row_end)
+// in multiples of 128 (a warp owns 128 consecutive rows of one column), no IB force band.  Same
+// device functions as lb_fused_v2, same bits; twice the bytes in flight per warp.  Used for the
+// pure-LB channel (C2) and for the rows above the force band of tall grids (C4).
+__global__ void __launch_bounds__(256, 2) lb_fused_v4(const LbParams p) {
+    const Lattice &L = p.L;
+    const int QP = ((p.row_end ? p.row_end : L.YDIM) - p.row_begin) >> 2;  // row quads per column
+    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (long long)p.col_count * QP) return;  // whole warps only
+    const int c = (int)(gid / QP);
+    const int yq = (int)(gid - (long long)c * QP);
+    int x = p.col_begin + c;
+    if (x >= p.split_at) x += p.split_skip;
+    const int y0 = p.row_begin + (yq << 2);
+    const int lane = threadIdx.x & 31;
+
+    Pulled4 q;
+    load_pulled4(L, p.src, x, y0, lane, q);
+    const bool forced = (p.gx != 0.0) | (p.gy != 0.0);
+    double n0[9], n1[9], n2[9], n3[9];
+    shift_pulled4(q, lane, n0, n1, n2, n3);
+    const double u0 = collide_node(n0, p.gx, p.gy, forced, p);
+    const double u1 = collide_node(n1, p.gx, p.gy, forced, p);
+    const double u2 = collide_node(n2, p.gx, p.gy, forced, p);
+    const double u3 = collide_node(n3, p.gx, p.gy, forced, p);
+    store_quad(p, x, y0, n0, n1, n2, n3);
+
+    // flux through x = XDIM-5: the summation tree of lb_fused_v2, bit for bit.  There a lane holds
+    // the pair sum of rows (2l, 2l+1) and the 32 pair sums of a 64-row slot are folded with offsets
+    // 16, 8, 4, 2, 1; here a lane holds two consecutive pair sums and a slot is 16 lanes: the same
+    // fold is offsets 8, 4, 2, 1 on each of the two, then their sum.
+    if (x == p.xq && p.qacc != nullptr) {
+        double s0 = u0 + u1, s1 = u2 + u3;
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {
+            s0 += __shfl_down_sync(0xffffffffu, s0, o);
+            s1 += __shfl_down_sync(0xffffffffu, s1, o);
+        }
+        if ((lane & 15) == 0) p.qacc[y0 >> 6] += (s0 + s1) / (double)L.YDIM;
     }
 }
 

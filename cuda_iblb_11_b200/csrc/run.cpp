@@ -5,10 +5,12 @@
 #include <sys/stat.h>
 #include <sys/types.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <condition_variable>
 #include <cstdlib>
+#include <cstring>
 #include <deque>
 #include <functional>
 #include <memory>
@@ -109,7 +111,141 @@ class SnapshotWriter {
 
 }  // namespace
 
-extern "C" int iblb_run(const iblb_params *pp, const char *root) {
+namespace {
+
+// Columns [x0, x0 + w) of slab r of n: equal split of the channel in units of `align` columns
+// (c_space with cilia, so that a cilium's base never sits on a seam), remainder to the low ranks.
+bool slab_range(int r, int n, unsigned XDIM, unsigned align, unsigned &x0, unsigned &w) {
+    if (align == 0) align = 1;
+    const unsigned units = XDIM / align;
+    if (units * align != XDIM || units < (unsigned)n) return false;
+    const unsigned base = units / n, rem = units % n;
+    w = (base + ((unsigned)r < rem ? 1 : 0)) * align;
+    x0 = ((unsigned)r * base + std::min((unsigned)r, rem)) * align;
+    return true;
+}
+
+// The channel of one run: the whole of it on one GPU, or x-slabs on several GPUs of this process
+// (iblb_connect_local: peer stores into the neighbours' ghost columns, CUDA events between the
+// slabs' streams), advanced in lockstep by this one host thread.  The reference's analogue is its
+// device selection (main.cu:395-396): it is single-GPU.
+struct Channel {
+    std::vector<iblb_solver *> slab;
+    std::vector<unsigned> x0, w;
+    unsigned XDIM = 0, YDIM = 0;
+
+    ~Channel() {
+        for (iblb_solver *s : slab) iblb_destroy(s);
+    }
+    int create(const iblb_params &p, int n_gpus, const char *restart_path) {
+        XDIM = p.XDIM;
+        YDIM = p.YDIM;
+        if (n_gpus <= 1) {
+            iblb_solver *s = nullptr;
+            int rc = iblb_create(&p, &s);
+            if (rc) return rc;
+            slab.push_back(s);
+            x0.push_back(0);
+            w.push_back(p.XDIM);
+            return restart_path ? iblb_load_checkpoint(s, restart_path) : IBLB_OK;
+        }
+        for (int r = 0; r < n_gpus; r++) {
+            iblb_params q = p;
+            unsigned a = 0, b = 0;
+            if (!slab_range(r, n_gpus, p.XDIM, p.c_num ? p.c_space : 1, a, b)) {
+                iblb::set_error("iblb_run: the channel cannot be cut into " + std::to_string(n_gpus) +
+                                " slabs of whole cilium spacings");
+                return IBLB_EINVAL;
+            }
+            q.slab_x0 = a;
+            q.slab_w = b;
+            // slab r on GPU (first + r); with fewer GPUs than slabs they share (same results: the
+            // slabs are ordered by events, not by where they run)
+            const int ndev = iblb_device_count();
+            q.device = ((p.device > 0 ? p.device : 0) + r) % (ndev > 0 ? ndev : 1);
+            iblb_solver *s = nullptr;
+            int rc = iblb_create(&q, &s);
+            if (rc) return rc;
+            slab.push_back(s);
+            x0.push_back(a);
+            w.push_back(b);
+            if (restart_path) {  // one file per slab, before the slabs are connected
+                rc = iblb_load_checkpoint(s, (std::string(restart_path) + "." + std::to_string(r)).c_str());
+                if (rc) return rc;
+            }
+        }
+        for (int r = 0; r < n_gpus; r++) {
+            int rc = iblb_connect_local(slab[r], slab[(r + n_gpus - 1) % n_gpus], slab[(r + 1) % n_gpus]);
+            if (rc) return rc;
+        }
+        return IBLB_OK;
+    }
+    unsigned iteration() const { return iblb_iteration(slab[0]); }
+    int step(unsigned n) {
+        if (slab.size() == 1) return iblb_step(slab[0], n);
+        for (unsigned k = 0; k < n; k++)  // lockstep: every slab one iteration, then the next
+            for (iblb_solver *s : slab) {
+                int rc = iblb_step(s, 1);
+                if (rc) return rc;
+            }
+        return IBLB_OK;
+    }
+    int sync() {
+        for (iblb_solver *s : slab) {
+            int rc = iblb_sync(s);
+            if (rc) return rc;
+        }
+        return IBLB_OK;
+    }
+    // rho[size], u[2*size] of the whole channel in the reference's layout (main.cu:944-952)
+    int fields(double *rho, double *u) {
+        if (slab.size() == 1) return iblb_get_fields(slab[0], rho, u);
+        const size_t size = (size_t)XDIM * YDIM;
+        std::vector<double> r, v;
+        for (size_t i = 0; i < slab.size(); i++) {
+            const size_t ls = (size_t)w[i] * YDIM;
+            r.resize(ls);
+            v.resize(2 * ls);
+            int rc = iblb_get_fields(slab[i], r.data(), v.data());
+            if (rc) return rc;
+            for (unsigned y = 0; y < YDIM; y++) {
+                const size_t g = (size_t)y * XDIM + x0[i], l = (size_t)y * w[i];
+                memcpy(rho + g, r.data() + l, sizeof(double) * w[i]);
+                memcpy(u + g, v.data() + l, sizeof(double) * w[i]);
+                memcpy(u + size + g, v.data() + ls + l, sizeof(double) * w[i]);
+            }
+        }
+        return IBLB_OK;
+    }
+    // every slab evaluates all cilia (prescribed kinematics): slab 0 speaks for them
+    int markers(float *pos, float *vel, int *eps) {
+        return iblb_get_markers(slab[0], pos, vel, nullptr, eps);
+    }
+    // the flux plane lives in exactly one slab; the others hold 0
+    int flux(double *Q) {
+        double q = 0.;
+        for (iblb_solver *s : slab) {
+            double v = 0.;
+            int rc = iblb_get_flux(s, &v);
+            if (rc) return rc;
+            q += v;
+        }
+        *Q = q;
+        return IBLB_OK;
+    }
+    int save(const char *path) {
+        if (slab.size() == 1) return iblb_save_checkpoint(slab[0], path);
+        for (size_t i = 0; i < slab.size(); i++) {
+            int rc = iblb_save_checkpoint(slab[i], (std::string(path) + "." + std::to_string(i)).c_str());
+            if (rc) return rc;
+        }
+        return IBLB_OK;
+    }
+};
+
+}  // namespace
+
+extern "C" int iblb_run_gpus(const iblb_params *pp, const char *root, int n_gpus) {
     using namespace std;
     if (!pp) return IBLB_EINVAL;
     iblb_params p = *pp;
@@ -154,18 +290,9 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
     cout << asctime(timeinfo) << endl;
     cout << "Initialising...\n";
 
-    iblb_solver *s = nullptr;
-    int rc = iblb_create(&p, &s);
+    Channel ch;  // destroys its solvers on every way out
+    int rc = ch.create(p, n_gpus, restart_path);
     if (rc) return rc;
-    if (restart_path) {
-        rc = iblb_load_checkpoint(s, restart_path);
-        if (rc) {
-            string keep = iblb_last_error();
-            iblb_destroy(s);
-            iblb::set_error(keep);
-            return rc;
-        }
-    }
 
     // ---- SimLog header, main.cu:761-790 ----
     const double l_0 = 0.000006, t_0 = 0.067;
@@ -193,13 +320,13 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
 
     // iteration `it` (0-based) is complete after it+1 steps; outputs follow iterations with
     // it % INTERVAL == 0 (main.cu:938); everything in between runs without host involvement
-    unsigned done = iblb_iteration(s);  // 0, or where the checkpoint was taken
+    unsigned done = ch.iteration();  // 0, or where the checkpoint was taken
     while (done < ITERATIONS && rc == IBLB_OK) {
         unsigned it_out;  // next iteration index whose completion triggers output
         if (INTERVAL == 0) it_out = ITERATIONS;  // no periodic output
         else it_out = ((done + INTERVAL - 1) / INTERVAL) * INTERVAL;
         unsigned target = (it_out < ITERATIONS) ? it_out + 1 : ITERATIONS;
-        rc = iblb_step(s, target - done);
+        rc = ch.step(target - done);
         if (rc) break;
         done = target;
         const unsigned it = done - 1;
@@ -213,9 +340,9 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
                 snap->sm.resize(2 * (size_t)Ns + 2);
                 snap->us.resize(2 * (size_t)Ns + 2);
                 snap->eps.resize((size_t)Ns + 1);
-                rc = iblb_get_fields(s, snap->rho.data(), snap->u.data());
+                rc = ch.fields(snap->rho.data(), snap->u.data());
                 if (rc) break;
-                rc = iblb_get_markers(s, snap->sm.data(), snap->us.data(), nullptr, snap->eps.data());
+                rc = ch.markers(snap->sm.data(), snap->us.data(), snap->eps.data());
                 if (rc) break;
                 const string fluid_file = raw_data + to_string(it) + "-fluid.dat";
                 const string cilia_file = cilia_data + to_string(it) + "-cilia.dat";
@@ -247,7 +374,7 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
                 });
             }
             double Q = 0.;
-            rc = iblb_get_flux(s, &Q);
+            rc = ch.flux(&Q);
             if (rc) break;
             fsB.open(flux.c_str(), ofstream::app);
             fsB << it * p.t_scale << "\t" << Q * p.x_scale << endl;  // main.cu:1002
@@ -262,7 +389,7 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
                      << endl;
             }
         }
-        if (ckpt_path && (rc = iblb_save_checkpoint(s, ckpt_path)) != IBLB_OK) break;
+        if (ckpt_path && (rc = ch.save(ckpt_path)) != IBLB_OK) break;
         if (it == INTERVAL && INTERVAL != 0) {  // main.cu:1007-1022
             const double cycle = now_seconds();
             time_t p_runtime = (time_t)((cycle - start) * (ITERATIONS / INTERVAL));
@@ -279,13 +406,13 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
     }
     if (rc == IBLB_OK) {
         double Q = 0.;
-        rc = iblb_get_flux(s, &Q);
+        rc = ch.flux(&Q);
         fsB.open(flux.c_str(), ofstream::app);
         fsB << ITERATIONS * p.t_scale << "\t" << Q * p.x_scale << endl;  // main.cu:1030-1034
         fsB.close();
     }
     string keep = iblb_last_error();
-    iblb_sync(s);
+    ch.sync();
     const double runtime = now_seconds() - start;  // main.cu:1038-1057
     int hours = 0, mins = 0;
     if (runtime > 3600) hours = (int)nearbyint(runtime / 3600 - 0.5);
@@ -303,8 +430,14 @@ extern "C" int iblb_run(const iblb_params *pp, const char *root) {
     // additions of this implementation (after the reference's last line)
     fsC << "MLUPS: " << (runtime > 0 ? (double)size * done / runtime / 1e6 : 0.) << endl;
     if (nonfinite_it >= 0) fsC << "Non-finite flux from output iteration: " << nonfinite_it << endl;
+    if (ch.slab.size() > 1) fsC << "GPUs: " << ch.slab.size() << " x-slabs" << endl;
     fsC.close();
-    iblb_destroy(s);
     if (rc) iblb::set_error(keep);
     return rc;
+}
+
+// main() as a whole on one GPU, or on IBLB_GPUS GPUs of this process when that is set
+extern "C" int iblb_run(const iblb_params *p, const char *root) {
+    const char *e = getenv("IBLB_GPUS");
+    return iblb_run_gpus(p, root, e ? atoi(e) : 1);
 }

@@ -194,7 +194,7 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
         set_error("iblb_create: LENGTH (markers per cilium) must be 1..128 and fine_points >= LENGTH");
         return IBLB_EINVAL;
     }
-    if (flux_back < 1 || flux_back > (int)p.XDIM) {
+    if (p.flux_back > p.XDIM) {  // (the default 5 on a narrower channel: no flux plane, as before)
         set_error("iblb_create: flux_back must be in 1..XDIM");
         return IBLB_EINVAL;
     }
@@ -231,6 +231,8 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
         return IBLB_EINVAL;
     }
     s->vec2 = (p.YDIM % 64 == 0);
+    s->vec4 = true;
+    if (const char *e = getenv("IBLB_V4")) s->vec4 = atoi(e) != 0;  // development A/B
     s->mpc = mpc;
     s->fine_points = fine_points;
     s->shape_scale = shape_scale;
@@ -402,6 +404,19 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
                 }
             }
             s->tiles_x = (L.W + s->tile_w - 1) / s->tile_w;
+            {
+                // Which single-launch form: the all-in-one tile CTA (two per SM) up to about one and
+                // a third waves, marker CTAs + light LB CTAs from there to four waves, where the heavy CTA's footprint
+                // costs more than the extra L2 round trips (measured: profiles/r02_time_small_*.log);
+                // IBLB_ROLES=0/1 overrides (development).
+                cudaDeviceProp prop;
+                int sms = 148;
+                if (cudaGetDeviceProperties(&prop, s->device) == cudaSuccess) sms = prop.multiProcessorCount;
+                const int rows = (L.YDIM / 64 > 8) ? s->band_tiles : L.YDIM / 64;
+                const double waves = (double)s->tiles_x * rows / (2. * sms);
+                s->roles = waves > 1.3 && waves <= 4.;
+                if (const char *e = getenv("IBLB_ROLES")) s->roles = atoi(e) != 0;
+            }
             // Capacity of the per-tile plans, decided here and not at run time: an upper bound on
             // the markers / cilia that can ever be within 1.5 of a tile, from the per-marker
             // envelopes (positions are wrapped into [0, XDIM], main.cu:193-196).  A carpet too
@@ -517,6 +532,15 @@ int iblb_sync(iblb_solver *s) {
 }
 
 unsigned iblb_iteration(const iblb_solver *s) { return s ? s->it : 0; }
+
+int iblb_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
 
 // Development: index violations counted on the device by an IBLB_CHECKED build (all solvers of the
 // current device, since start); -1 when the library was built without the checks.

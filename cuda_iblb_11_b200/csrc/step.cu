@@ -53,8 +53,14 @@ struct PhaseEvents {
 // Launch the fused LB kernel over the column range encoded in q.
 int launch_lb(iblb_solver *s, const LbParams &q, cudaStream_t st, unsigned long long &launches) {
     if (q.col_count <= 0) return IBLB_OK;
-    if (s->vec2) {
-        const long long n = (long long)q.col_count * ((s->L.YDIM - q.row_begin) / 2);
+    const int rows = (q.row_end ? q.row_end : s->L.YDIM) - q.row_begin;
+    if (s->vec2 && s->vec4 && q.band == nullptr && rows % 128 == 0 && q.col_count >= 64) {
+        // four nodes per thread, 256-bit accesses: no force band on these rows
+        const long long n = (long long)q.col_count * (rows / 4);
+        lb_fused_v4<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(q);
+        launches += 1;
+    } else if (s->vec2) {
+        const long long n = (long long)q.col_count * (rows / 2);
         lb_fused_v2<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(q);
         launches += 1;
     } else {
@@ -188,7 +194,9 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
             bp.it_ptr = s->it_dev;
             bp.it = graph_it_off;
         }
-        dim3 g((unsigned)(bp.n_marker + bp.rows_lb * s->tiles_x));
+        // one CTA per tile (row tiles x column tiles), or marker CTAs followed by LB CTAs
+        dim3 g = s->roles ? dim3((unsigned)(bp.n_marker + bp.rows_lb * s->tiles_x))
+                          : dim3((unsigned)bp.rows_lb, (unsigned)s->tiles_x);
         // Programmatic dependent launch behind the previous iteration's lb_ib_tile_step: the
         // marker CTAs' fluid-independent prologue overlaps that kernel's tail.  Not right behind the
         // kernels that write what the prologue reads (kinematics, tile lists), and not on tall
@@ -205,7 +213,8 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         const bool pdl = !split && !fresh_plan && chain && !(s->p.flags & IBLB_FLAG_NO_PDL);
         cfg.attrs = &attr;
         cfg.numAttrs = pdl ? 1 : 0;
-        IBLB_CUDA(cudaLaunchKernelEx(&cfg, lb_ib_tile_step, bp));
+        if (s->roles) IBLB_CUDA(cudaLaunchKernelEx(&cfg, lb_ib_roles_step, bp));
+        else IBLB_CUDA(cudaLaunchKernelEx(&cfg, lb_ib_tile_step, bp));
         s->pdl_chain = !split;
         launches += 1;
         if (split) {

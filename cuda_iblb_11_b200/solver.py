@@ -107,7 +107,8 @@ SYMBOLS = [
     "iblb_set_fields", "iblb_marker_fine_index", "iblb_last_step_seconds",
     "iblb_last_step_launches", "iblb_profile_phases", "iblb_export_halo", "iblb_connect",
     "iblb_connect_local", "iblb_set_marker_replay", "iblb_run", "iblb_last_error", "iblb_version",
-    "iblb_save_checkpoint", "iblb_load_checkpoint", "iblb_debug_violations",
+    "iblb_save_checkpoint", "iblb_load_checkpoint", "iblb_debug_violations", "iblb_run_gpus",
+    "iblb_device_count",
 ]
 
 
@@ -152,6 +153,7 @@ def lib():
     L.iblb_set_marker_replay.argtypes = [vp, ctypes.c_uint, vp, ctypes.c_uint]
     L.iblb_run.argtypes = [ctypes.POINTER(Params), ctypes.c_char_p]
     L.iblb_debug_violations.restype = ctypes.c_longlong
+    L.iblb_run_gpus.argtypes = [ctypes.POINTER(Params), ctypes.c_char_p, ctypes.c_int]
     _lib = L
     return L
 
@@ -291,6 +293,11 @@ def debug_violations():
     return lib().iblb_debug_violations()
 
 
-def run(params, root=None):
-    """The whole reference program (main.cu) for `params`: steps + Data/ tree under `root`."""
-    _check(lib().iblb_run(ctypes.byref(params), None if root is None else str(root).encode()))
+def run(params, root=None, gpus=None):
+    """The whole reference program (main.cu) for `params`: steps + Data/ tree under `root`;
+    `gpus`: x-slabs over that many GPUs of this process (None: IBLB_GPUS or 1)."""
+    r = None if root is None else str(root).encode()
+    if gpus is None:
+        _check(lib().iblb_run(ctypes.byref(params), r))
+    else:
+        _check(lib().iblb_run_gpus(ctypes.byref(params), r, gpus))

@@ -173,6 +173,15 @@ int iblb_load_checkpoint(iblb_solver *s, const char *path);
 /* Runs ITERATIONS steps writing the reference's Data/ tree under `root` (NULL: "Data/").
  * main.cu:589-631, 758-790, 936-1005, 1030-1060. */
 int iblb_run(const iblb_params *p, const char *root);
+/* The same on n_gpus GPUs of this process: the channel is cut into n_gpus x-slabs (whole cilium
+ * spacings each) on devices p->device, p->device+1, ... (wrapping when the machine has fewer),
+ * coupled by iblb_connect_local and advanced in lockstep by the calling thread; fields are gathered
+ * into the same files, the flux comes from the slab that owns the flux plane, a checkpoint is one
+ * file per slab (<path>.<slab>).  iblb_run takes n_gpus from the environment (IBLB_GPUS, default 1);
+ * the reference is single-GPU (device selection: main.cu:395-396). */
+int iblb_run_gpus(const iblb_params *p, const char *root, int n_gpus);
+/* CUDA devices visible to this process (0 when the runtime cannot be initialised). */
+int iblb_device_count(void);
 
 /* Development: device-side index violations counted by a library built with IBLB_CHECKED=1
  * (range checks on every population / band / marker / shared-table index); -1 in product builds. */

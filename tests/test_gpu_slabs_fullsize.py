@@ -236,6 +236,58 @@ def test_run_restarts_from_a_checkpoint(tmp_path, monkeypatch):
 
 
 
+@pytest.mark.parametrize("n_slabs", [2, 3])
+def test_run_on_several_gpus_writes_the_same_tree(tmp_path, n_slabs):
+    """iblb_run_gpus / `IBLB_GPUS=N ./app ...`: the C++ driver cuts the channel into N x-slabs on
+    the GPUs of this process (wrapping onto the GPUs there are), couples them with
+    iblb_connect_local, steps them in lockstep and gathers the snapshots: every file of the Data/
+    tree is byte-identical to the one-GPU run's (SimLog aside: timings).  Checkpoints are one file
+    per slab and restart the same way."""
+    def params(iterations):
+        p = Params.from_args("6 6 48 1.0 1.0 5 1.0 100 0 1".split())
+        p.ITERATIONS, p.INTERVAL, p.device = iterations, 20, 0
+        return p
+    one, many, part = str(tmp_path / "one"), str(tmp_path / "many"), str(tmp_path / "part")
+    run(params(41), one, gpus=1)
+    run(params(41), many, gpus=n_slabs)
+    names = [("Raw/6/6", "0-fluid.dat"), ("Raw/6/6", "20-fluid.dat"), ("Raw/6/6", "40-fluid.dat"),
+             ("Cilia/6/6", "20-cilia.dat"), ("Cilia/6/6", "40-cilia.dat"),
+             ("Flux", "6_6_48_1_1x5-flux.dat")]
+    for sub, name in names:
+        assert open(os.path.join(one, sub, name)).read() == open(os.path.join(many, sub, name)).read(), name
+    assert "GPUs: %d x-slabs" % n_slabs in open(os.path.join(many, "Raw/6/6", "SimLog.txt")).read()
+    # checkpoint after 21 iterations on N slabs, restart on N slabs, same final files
+    ck = str(tmp_path / "run.ckp")
+    os.environ["IBLB_CHECKPOINT"] = ck
+    try:
+        run(params(21), part, gpus=n_slabs)
+    finally:
+        del os.environ["IBLB_CHECKPOINT"]
+    assert all(os.path.exists("%s.%d" % (ck, r)) for r in range(n_slabs))
+    os.environ["IBLB_RESTART"] = ck
+    try:
+        run(params(41), part, gpus=n_slabs)
+    finally:
+        del os.environ["IBLB_RESTART"]
+    for sub, name in (("Raw/6/6", "40-fluid.dat"), ("Cilia/6/6", "40-cilia.dat")):
+        assert open(os.path.join(one, sub, name)).read() == open(os.path.join(part, sub, name)).read()
+
+
+def test_app_runs_on_several_gpus_from_the_environment(tmp_path):
+    app = os.path.join(ROOT, "app")
+    if not os.path.exists(app):
+        pytest.skip("app not built")
+    outs = []
+    for gpus in ("1", "2"):
+        env = dict(os.environ, IBLB_ROOT=str(tmp_path / ("D" + gpus)), IBLB_ITERATIONS="30",
+                   IBLB_GPUS=gpus)
+        r = subprocess.run([app] + "6 6 48 1.0 1.0 5 1.0 100 0 0".split(), capture_output=True,
+                           text=True, env=env)
+        assert r.returncode == 0, r.stderr
+        outs.append(open(str(tmp_path / ("D" + gpus) / "Flux" / "6_6_48_1_1x5-flux.dat")).read())
+    assert outs[0] == outs[1] and len(outs[0].splitlines()) >= 1
+
+
 def test_app_executable_surface(tmp_path):
     app = os.path.join(ROOT, "app")
     if not os.path.exists(app):

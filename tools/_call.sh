@@ -1,4 +1,3 @@
 mkdir -p gpurun_out
-timeout 300 python tools/time_small.py 4 > gpurun_out/r02_time_small_roles.log 2>&1; echo "small rc=$?"; cat gpurun_out/r02_time_small_roles.log
-timeout 900 python -m pytest tests -m gpu -q --timeout 600 -x > gpurun_out/r02_pytest_gpu_roles.log 2>&1; echo "pytest rc=$?"; tail -n 25 gpurun_out/r02_pytest_gpu_roles.log
-IBLB_TAG=r02 bash tools/gpu_sanitize.sh
+timeout 300 python -m pytest tests/test_gpu_parity.py -m gpu -q --timeout 600 -k "four_node or tall or rest_state" > gpurun_out/r02_pytest_v4.log 2>&1; echo "pytest rc=$?"; tail -n 8 gpurun_out/r02_pytest_v4.log
+timeout 600 python tools/ab_c2.py > gpurun_out/r02_ab_v2_v4.log 2>&1; cat gpurun_out/r02_ab_v2_v4.log

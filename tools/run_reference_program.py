@@ -67,7 +67,7 @@ def read_table(path):
 
 
 def compare_simlog(a, b):
-    skip = ("Completion time", "Total runtime", "MLUPS", "Non-finite flux")
+    skip = ("Completion time", "Total runtime", "MLUPS", "Non-finite flux", "GPUs:")
     la = [l.rstrip("\n") for l in open(a)]
     lb = [l.rstrip("\n") for l in open(b)]
     la = [l for l in la[1:] if l.strip() and not l.startswith(skip)]

@@ -23,11 +23,20 @@ def t_step(p, n, warm):
 
 if __name__ == "__main__":
     cases = [(288, 192, 6, 48, 4000), (576, 192, 12, 48, 4000), (2304, 192, 48, 48, 2000),
-             (8192, 192, 64, 128, 1000), (8192, 2048, 64, 128, 200), (8192, 8192, 64, 128, 40)]
+             (8192, 192, 64, 128, 1000), (1152, 192, 24, 48, 3000), (4608, 192, 96, 48, 1500),
+             (8192, 2048, 64, 128, 200), (8192, 8192, 64, 128, 40)]
     if len(sys.argv) > 1:
         cases = cases[:int(sys.argv[1])]
     for (X, Y, cn, cs, n) in cases:
         kw = dict(c_num=cn, c_space=cs, c_fraction=cn)
+        # both single-launch forms (iblb_create picks one by the grid's wave count; IBLB_ROLES forces)
+        os.environ["IBLB_ROLES"] = "0"
+        t_tile = t_step(Params.channel(X, Y, **kw), n, 50)
+        os.environ["IBLB_ROLES"] = "1"
+        t_roles = t_step(Params.channel(X, Y, **kw), n, 50)
+        del os.environ["IBLB_ROLES"]
+        print("      single-launch forms: all-in-one tile CTA %.2f us, marker CTAs + LB CTAs %.2f us" % (
+            t_tile, t_roles), flush=True)
         fused = t_step(Params.channel(X, Y, **kw), n, 50)
         fused_direct = t_step(Params.channel(X, Y, flags=FLAG_NO_GRAPH, **kw), n, 50)
         chain = t_step(Params.channel(X, Y, flags=FLAG_NO_FUSE, **kw), n, 50)
