@@ -169,13 +169,14 @@ int iblb_load_checkpoint(iblb_solver *s, const char *path) {
     // step flags of a slab that gets connected later carry flag_base + it (solver.cu: init_state)
     s->flag_base += (int)s->it - (int)it;
     s->it = it;
+    s->hist_from = it;  // the flux history is not part of a checkpoint
     s->cur = cur;
     if (s->it_dev) IBLB_CUDA(cudaMemcpy(s->it_dev, &it, sizeof(int), cudaMemcpyHostToDevice));
     // marker slots and tile plans are rebuilt by the next step; F_s and the force band of the last
     // completed iteration by the next getter (from the buffer that iteration pulled from)
     s->kin_base = -1;
     s->lists_base = -1;
-    if (s->tile_flag)  // iteration-numbered flags of the fused step: the iteration may have gone back
+    if (s->tile_flag)  // iteration-numbered flags of the role-split step: the iteration may have gone back
         IBLB_CUDA(cudaMemset(s->tile_flag, 0, sizeof(int) * (size_t)s->band_tiles * s->tiles_x));
     s->pdl_chain = false;
     s->ib_stale = s->p.c_num > 0 && it > 0;

@@ -548,7 +548,7 @@ __device__ __forceinline__ void lb_cta(const BandParams &p, int b) {
         double s = ux0 + ux1;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
-        if (lane == 0) lp.qacc[tile_y] += s / (double)L.YDIM;
+        if (lane == 0) flux_add(lp, tile_y, s / (double)L.YDIM);
     }
 }
 
@@ -698,7 +698,7 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
         double s = ux0 + ux1;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
-        if (lane == 0) lp.qacc[tile_y] += s / (double)L.YDIM;
+        if (lane == 0) flux_add(lp, tile_y, s / (double)L.YDIM);
     }
 }
 

@@ -46,6 +46,7 @@ constexpr int kFinePoints = 9600;       // main.cu:81
 constexpr double kShapeScale = 111.;    // main.cu:137-145
 constexpr int kSpreadTileX = 8, kSpreadTileY = 32;
 constexpr int kKinBatch = 32;      // iterations of marker kinematics computed per launch
+constexpr int kFluxHist = 4096;  // iterations of per-step flux the solver keeps (iblb_get_flux_history)
 constexpr int kSlabFlags = 4;  // slab step counters: [0],[1] data ready from the left / right neighbour; [2],[3] their release
 constexpr int kMaxLeftCilia = 16;  // r_max = 2*96/c_space (main.cu:185) must not exceed this
 
@@ -86,6 +87,11 @@ struct LbParams {
     double half;                     // 0.5 when the half-force velocity applies, else 0
     double *qacc;                    // per-warp running flux sums [YDIM/64] or nullptr
     int xq;                          // local column of the flux plane (XDIM-5) or -1000
+    // flux history: row (iteration % kFluxHist) of qhist [kFluxHist][nq] receives the running sums
+    // as they stand after this iteration; iteration = (it_ptr ? *it_ptr : 0) + it
+    double *qhist;
+    const int *it_ptr;
+    int it, nq;
     // columns this launch covers: c in [0, col_count) -> x = col_begin + c, and x += split_skip
     // when x >= split_at (boundary launch = the first and last G columns in one grid)
     int col_begin, col_count, split_at, split_skip;

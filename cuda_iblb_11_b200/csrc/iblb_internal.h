@@ -22,7 +22,8 @@ int cuda_fail(cudaError_t e, const char *what);
 __global__ void lb_fused_v2(const LbParams p);
 __global__ void lb_fused_v4(const LbParams p);
 __global__ void lb_fused_v1(const LbParams p, double *qpart);
-__global__ void flux_reduce_v1(const double *qpart, int n, double *qacc);
+__global__ void flux_reduce_v1(const double *qpart, int n, double *qacc, double *qhist,
+                               const int *it_ptr, int it);
 __global__ void lb_init(const LbParams p, const double *rho_in, const double *u_in, double u0_amp,
                         int row0, int nrows);
 __global__ void halo_push(const Lattice L, const double *buf, Remote left, Remote right);
@@ -75,7 +76,7 @@ struct iblb_solver {
     bool ib_stale;             // F_s / force band not materialised for the last step
     bool pdl_chain;            // the last kernel enqueued was lb_ib_tile_step over the whole grid
     iblb::TileProgram *prog;   // per slot and band tile: fluid-independent plan (ib_tile_lists)
-    bool roles;                // lb_ib_roles_step (marker CTAs + LB CTAs) instead of lb_ib_tile_step
+    int form;                  // single-launch IB+LB iteration: 0 lb_ib_tile_step, 1 lb_ib_roles_step
     int tile_w;                // columns per tile of lb_ib_tile_step: 8, or 6 where that fills the SMs better
     int tiles_x, band_tiles;   // column tiles, band row tiles
     int *tile_flag;            // per band tile: iteration + 1 whose force the band buffer holds
@@ -88,6 +89,9 @@ struct iblb_solver {
     int replay_steps, replay_j;
     // flux
     double *qacc, *qpart;
+    double *qhist;             // [kFluxHist][nq] running flux sums after each of the last iterations
+    unsigned hist_from;        // first iteration whose row of qhist is valid (restart point)
+    int cap_off;               // >= 0 while a graph batch is being captured: offset within the batch
     double *q_host;            // pinned: nq flux partial sums + the device error flag (one sync)
     double *stage_dev;         // kStageDoubles: row chunks of fields on their way to / from the host
     int nq;

@@ -96,6 +96,18 @@ __device__ __forceinline__ double collide_node(double (&f)[9], double Fx, double
     return ux;
 }
 
+// running flux sum of one 64-row slot (ImmersedBoundary.cu:259-264: Q is cumulative), and its value
+// after this iteration into the history ring (the reference copies Q back every step, main.cu:928;
+// here a caller reads a whole interval at once: iblb_get_flux_history)
+__device__ __forceinline__ void flux_add(const LbParams &p, int slot, double v) {
+    const double q = p.qacc[slot] + v;
+    p.qacc[slot] = q;
+    if (p.qhist != nullptr) {
+        const int it = (p.it_ptr ? __ldcg(p.it_ptr) : 0) + p.it;
+        p.qhist[(long long)(it % kFluxHist) * p.nq + slot] = q;
+    }
+}
+
 __device__ __forceinline__ void store_remote2(const Remote &r, int col, int y0, int i, double2 v) {
     IBLB_CHK(col + r.G >= 0 && col + r.G < r.W + 2 * r.G && y0 >= 0 && y0 + 1 < r.ld && i >= 0 && i < 9);
     *reinterpret_cast<double2 *>(r.base + (long long)i * r.plane + (long long)(col + r.G) * r.ld +

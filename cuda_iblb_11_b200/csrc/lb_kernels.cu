@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(256, 3) lb_fused_v2(const LbParams p) {
         double s = ux0 + ux1;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
-        if (lane == 0) p.qacc[y0 >> 6] += s / (double)L.YDIM;
+        if (lane == 0) flux_add(p, y0 >> 6, s / (double)L.YDIM);
     }
 }
 
@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(256, 2) lb_fused_v4(const LbParams p) {
             s0 += __shfl_down_sync(0xffffffffu, s0, o);
             s1 += __shfl_down_sync(0xffffffffu, s1, o);
         }
-        if ((lane & 15) == 0) p.qacc[y0 >> 6] += (s0 + s1) / (double)L.YDIM;
+        if ((lane & 15) == 0) flux_add(p, y0 >> 6, (s0 + s1) / (double)L.YDIM);
     }
 }
 
@@ -166,7 +166,8 @@ __global__ void __launch_bounds__(256) lb_fused_v1(const LbParams p, double *qpa
 }
 
 // generic path's deterministic flux reduction: one block, fixed strided order + fixed tree
-__global__ void flux_reduce_v1(const double *qpart, int n, double *qacc) {
+__global__ void flux_reduce_v1(const double *qpart, int n, double *qacc, double *qhist,
+                               const int *it_ptr, int it) {
     __shared__ double sh[256];
     double v = 0.;
     for (int y = threadIdx.x; y < n; y += 256) v += qpart[y];
@@ -176,7 +177,11 @@ __global__ void flux_reduce_v1(const double *qpart, int n, double *qacc) {
         if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
         __syncthreads();
     }
-    if (threadIdx.x == 0) qacc[0] += sh[0];
+    if (threadIdx.x == 0) {
+        const double q = qacc[0] + sh[0];
+        qacc[0] = q;
+        if (qhist != nullptr) qhist[((it_ptr ? *it_ptr : 0) + it) % kFluxHist] = q;  // nq == 1
+    }
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -65,6 +65,15 @@ LbParams make_lb_params(const iblb_solver *s, int src_idx) {
     const bool half = s->p.c_num > 0 || (s->p.flags & IBLB_FLAG_HALF_FORCE_BODY);
     q.half = half ? 0.5 : 0.0;
     q.qacc = s->flux_on ? s->qacc : nullptr;
+    q.qhist = s->flux_on ? s->qhist : nullptr;
+    q.nq = s->nq;
+    if (s->cap_off >= 0) {  // captured batches read the iteration number from the device
+        q.it_ptr = s->it_dev;
+        q.it = s->cap_off;
+    } else {
+        q.it_ptr = nullptr;
+        q.it = (int)s->it;
+    }
     q.xq = s->flux_on ? s->xq_local : -1000;
     q.col_begin = 0;
     q.col_count = s->L.W;
@@ -162,6 +171,7 @@ static int init_state(iblb_solver *s, const double *rho, const double *u) {
     s->lists_base = -1;
     s->flag_base += (int)s->it;  // all slabs reset together: later flag values stay above old ones
     s->it = 0;
+    s->hist_from = 0;
     IBLB_CUDA(cudaStreamSynchronize(s->stream));
     return IBLB_OK;
 }
@@ -251,6 +261,8 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
     if (rc == IBLB_OK) TRY(cudaMemset(s->buf[1], 0, pop_bytes));
     s->nq = s->vec2 ? (int)p.YDIM / 64 : 1;
     TRY(cudaMalloc((void **)&s->qacc, sizeof(double) * s->nq));
+    TRY(cudaMalloc((void **)&s->qhist, sizeof(double) * s->nq * (size_t)kFluxHist));
+    s->cap_off = -1;
     TRY(cudaMallocHost((void **)&s->q_host, sizeof(double) * (s->nq + 1)));
     if (!s->vec2) TRY(cudaMalloc((void **)&s->qpart, sizeof(double) * p.YDIM));
     TRY(cudaMalloc((void **)&s->flags, kSlabFlags * sizeof(int)));
@@ -405,17 +417,23 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
             }
             s->tiles_x = (L.W + s->tile_w - 1) / s->tile_w;
             {
-                // Which single-launch form: the all-in-one tile CTA (two per SM) up to about one and
-                // a third waves, marker CTAs + light LB CTAs from there to four waves, where the heavy CTA's footprint
-                // costs more than the extra L2 round trips (measured: profiles/r02_time_small_*.log);
-                // IBLB_ROLES=0/1 overrides (development).
+                // Which single-launch form (bit-identical; measured in profiles/r02_time_small_*.log),
+                // by how many waves of all-in-one tile CTAs (two per SM) the grid would be:
+                //   up to 1.3 and beyond 4   lb_ib_tile_step: the tile's CTA does everything (the
+                //                            reference's own scripts are well under one wave);
+                //   1.3 .. 4                 lb_ib_roles_step: marker CTAs + light LB CTAs.
+                // Tall grids (only the band's tiles in the IB kernel, the rest in lb_fused_v2/v4)
+                // keep the first.  IBLB_FORM=0/1 overrides (development).  A third form — ib_interp
+                // and a per-tile spreading kernel beside two LB launches on two streams — was
+                // measured and dropped (profiles/r02_form2_dead_end.md).
                 cudaDeviceProp prop;
                 int sms = 148;
                 if (cudaGetDeviceProperties(&prop, s->device) == cudaSuccess) sms = prop.multiProcessorCount;
-                const int rows = (L.YDIM / 64 > 8) ? s->band_tiles : L.YDIM / 64;
+                const bool tall = L.YDIM / 64 > 8;
+                const int rows = tall ? s->band_tiles : L.YDIM / 64;
                 const double waves = (double)s->tiles_x * rows / (2. * sms);
-                s->roles = waves > 1.3 && waves <= 4.;
-                if (const char *e = getenv("IBLB_ROLES")) s->roles = atoi(e) != 0;
+                s->form = (!tall && waves > 1.3 && waves <= 4.) ? 1 : 0;
+                if (const char *e = getenv("IBLB_FORM")) s->form = atoi(e) == 1 ? 1 : 0;
             }
             // Capacity of the per-tile plans, decided here and not at run time: an upper bound on
             // the markers / cilia that can ever be within 1.5 of a tile, from the per-marker
@@ -494,7 +512,7 @@ int iblb_destroy(iblb_solver *s) {
             if (s->nb_mapped[f][b]) cudaIpcCloseMemHandle(s->nb_mapped[f][b]);
         if (s->nb_flag_mapped[f]) cudaIpcCloseMemHandle(s->nb_flag_mapped[f]);
     }
-    cudaFree(s->buf[0]); cudaFree(s->buf[1]); cudaFree(s->qacc); cudaFree(s->qpart);
+    cudaFree(s->buf[0]); cudaFree(s->buf[1]); cudaFree(s->qacc); cudaFree(s->qpart); cudaFree(s->qhist);
     if (s->q_host) cudaFreeHost(s->q_host);
     cudaFree(s->stage_dev);
     cudaFree(s->flags); cudaFree(s->band); cudaFree(s->M.s); cudaFree(s->M.u_s);

@@ -77,7 +77,7 @@ int launch_lb(iblb_solver *s, const LbParams &q, cudaStream_t st, unsigned long 
             else
                 covered = c >= q.col_begin && c < q.col_begin + q.col_count;
             if (covered) {
-                flux_reduce_v1<<<1, 256, 0, st>>>(s->qpart, s->L.YDIM, s->qacc);
+                flux_reduce_v1<<<1, 256, 0, st>>>(s->qpart, s->L.YDIM, s->qacc, q.qhist, q.it_ptr, q.it);
                 launches += 1;
             }
         }
@@ -96,6 +96,7 @@ int launch_lb(iblb_solver *s, const LbParams &q, cudaStream_t st, unsigned long 
 int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEvents *pe,
                       unsigned long long &launches, int graph_it_off = 0) {
     const int src = s->cur;
+    s->cap_off = graph_mode ? graph_it_off : -1;  // make_lb_params: where the iteration number lives
     const bool coupled = s->connected && !(s->self_left && s->self_right);
     const bool local = coupled && s->peer[0] != nullptr;
     // Slabs coupled across processes run two streams: `sb` carries what the neighbours wait for
@@ -195,7 +196,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
             bp.it = graph_it_off;
         }
         // one CTA per tile (row tiles x column tiles), or marker CTAs followed by LB CTAs
-        dim3 g = s->roles ? dim3((unsigned)(bp.n_marker + bp.rows_lb * s->tiles_x))
+        dim3 g = s->form == 1 ? dim3((unsigned)(bp.n_marker + bp.rows_lb * s->tiles_x))
                           : dim3((unsigned)bp.rows_lb, (unsigned)s->tiles_x);
         // Programmatic dependent launch behind the previous iteration's lb_ib_tile_step: the
         // marker CTAs' fluid-independent prologue overlaps that kernel's tail.  Not right behind the
@@ -213,7 +214,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         const bool pdl = !split && !fresh_plan && chain && !(s->p.flags & IBLB_FLAG_NO_PDL);
         cfg.attrs = &attr;
         cfg.numAttrs = pdl ? 1 : 0;
-        if (s->roles) IBLB_CUDA(cudaLaunchKernelEx(&cfg, lb_ib_roles_step, bp));
+        if (s->form == 1) IBLB_CUDA(cudaLaunchKernelEx(&cfg, lb_ib_roles_step, bp));
         else IBLB_CUDA(cudaLaunchKernelEx(&cfg, lb_ib_tile_step, bp));
         s->pdl_chain = !split;
         launches += 1;
@@ -272,6 +273,7 @@ int build_graph(iblb_solver *s) {
     for (unsigned i = 0; i < kGraphBatch && rc == IBLB_OK; i++)
         rc = enqueue_iteration(s, s->stream, true, nullptr, dummy, (int)i);
     if (rc == IBLB_OK && s->it_dev) it_advance<<<1, 32, 0, s->stream>>>(s->it_dev, (int)kGraphBatch);
+    s->cap_off = -1;
     cudaError_t e = cudaStreamEndCapture(s->stream, &graph);
     s->graph_launches = dummy + (s->it_dev ? 1 : 0);
     s->cur = cur0;
@@ -378,7 +380,7 @@ int iblb_step(iblb_solver *s, unsigned n_steps) {
             if (s->p.c_num > 0) {
                 s->ib_stale = fused_path(s);
                 s->kin_base = (long long)s->it - kGraphBatch;
-                s->lists_base = s->ib_stale ? s->kin_base : -1;
+                s->lists_base = fused_path(s) ? s->kin_base : -1;
             }
         }
     }
@@ -545,6 +547,38 @@ int iblb_get_flux(iblb_solver *s, double *Q) {
     double q = 0.;
     for (int i = 0; i < s->nq; i++) q += part[i];  // fixed slot order
     *Q = q;
+    return IBLB_OK;
+}
+
+// Q after each of the iterations first_it .. first_it + n - 1 (0-based), i.e. what the reference's
+// per-step copy of d_Q (main.cu:928) would have delivered, without a synchronisation per step.
+int iblb_get_flux_history(iblb_solver *s, unsigned first_it, unsigned n, double *Q) {
+    if (!s || !Q || n == 0) return IBLB_EINVAL;
+    if ((unsigned long long)first_it + n > s->it || s->it - first_it > (unsigned)kFluxHist ||
+        first_it < s->hist_from) {
+        set_error("iblb_get_flux_history: the solver keeps the last 4096 completed iterations "
+                  "(since the last restart)");
+        return IBLB_EINVAL;
+    }
+    IBLB_CUDA(cudaSetDevice(s->device));
+    if (!s->flux_on) {  // no flux plane in this solver (no cilia, or another slab owns it)
+        for (unsigned i = 0; i < n; i++) Q[i] = 0.;
+        return iblb_sync(s);
+    }
+    std::vector<double> rows((size_t)n * s->nq);
+    for (unsigned done = 0; done < n;) {  // the ring may wrap once
+        const unsigned r0 = (first_it + done) % kFluxHist;
+        const unsigned len = std::min<unsigned>(n - done, kFluxHist - r0);
+        IBLB_CUDA(cudaMemcpyAsync(rows.data() + (size_t)done * s->nq, s->qhist + (size_t)r0 * s->nq,
+                                  sizeof(double) * len * s->nq, cudaMemcpyDeviceToHost, s->stream));
+        done += len;
+    }
+    IBLB_CUDA(cudaStreamSynchronize(s->stream));
+    for (unsigned i = 0; i < n; i++) {
+        double q = 0.;
+        for (int k = 0; k < s->nq; k++) q += rows[(size_t)i * s->nq + k];  // fixed slot order
+        Q[i] = q;
+    }
     return IBLB_OK;
 }
 

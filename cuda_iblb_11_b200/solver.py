@@ -108,7 +108,7 @@ SYMBOLS = [
     "iblb_last_step_launches", "iblb_profile_phases", "iblb_export_halo", "iblb_connect",
     "iblb_connect_local", "iblb_set_marker_replay", "iblb_run", "iblb_last_error", "iblb_version",
     "iblb_save_checkpoint", "iblb_load_checkpoint", "iblb_debug_violations", "iblb_run_gpus",
-    "iblb_device_count",
+    "iblb_device_count", "iblb_get_flux_history",
 ]
 
 
@@ -141,6 +141,7 @@ def lib():
     L.iblb_get_markers.argtypes = [vp, vp, vp, vp, vp]
     L.iblb_get_flux.argtypes = [vp, dp]
     L.iblb_set_fields.argtypes = [vp, vp, vp]
+    L.iblb_get_flux_history.argtypes = [vp, ctypes.c_uint, ctypes.c_uint, vp]
     L.iblb_save_checkpoint.argtypes = [vp, ctypes.c_char_p]
     L.iblb_load_checkpoint.argtypes = [vp, ctypes.c_char_p]
     L.iblb_marker_fine_index.argtypes = [vp, ctypes.c_uint]
@@ -217,6 +218,13 @@ class Solver:
         q = ctypes.c_double()
         _check(lib().iblb_get_flux(self._h, ctypes.byref(q)))
         return q.value
+
+    def flux_history(self, first_it, n):
+        """Q after each of the iterations first_it .. first_it+n-1 (the reference's per-step Q,
+        main.cu:928) from the device-side history: one copy, one synchronisation."""
+        q = np.empty(n)
+        _check(lib().iblb_get_flux_history(self._h, first_it, n, q.ctypes.data))
+        return q
 
     def set_fields(self, rho, u):
         rho = np.ascontiguousarray(rho, np.float64)

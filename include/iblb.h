@@ -119,6 +119,10 @@ int iblb_get_markers(iblb_solver *s, float *pos, float *vel, float *force /*2*Ns
                      int *eps /*Ns*/);
 /* cumulative flux Q of main.cu:928 / ImmersedBoundary.cu:259-264 */
 int iblb_get_flux(iblb_solver *s, double *Q);
+/* Q as it stood after each of the iterations first_it .. first_it+n-1 (0-based): the values the
+ * reference's per-step copy of d_Q delivers (main.cu:928), kept on the device for the last 4096
+ * completed iterations, so that a caller who wants Q every step need not synchronise every step. */
+int iblb_get_flux_history(iblb_solver *s, unsigned first_it, unsigned n, double *Q /*n*/);
 /* Replace the state by the equilibrium of (rho,u) as main.cu:722-754 does for rho=1,u=0;
  * resets the iteration counter and Q.  Host arrays, reference layout. */
 int iblb_set_fields(iblb_solver *s, const double *rho, const double *u);

@@ -569,6 +569,44 @@ def test_tall_grid_split_step_equals_separate_kernels_and_oracle(c_num, c_space,
     o.close()
 
 
+@pytest.mark.parametrize("form", ["0", "1"])
+@pytest.mark.parametrize("c_num,c_space,c_fraction,Y", [
+    (6, 48, 6, 192), (12, 48, 5, 192), (5, 44, 5, 192), (16, 128, 16, 128), (48, 48, 48, 192),
+])
+def test_every_form_of_the_iteration_is_bit_identical(form, c_num, c_space, c_fraction, Y,
+                                                      monkeypatch, tmp_path):
+    """iblb_create picks one of two forms of the single-launch IB+LB iteration by the size of the
+    grid (all-in-one tile CTA / marker CTAs + LB CTAs); IBLB_FORM forces each of them here, on small and wide grids, with
+    CUDA-graph batches and with direct launches, through a checkpoint and back: always the state of
+    the unfused chain, bit for bit."""
+    X = c_num * c_space
+    kw = dict(c_num=c_num, c_space=c_space, c_fraction=c_fraction)
+    monkeypatch.setenv("IBLB_FORM", form)
+    a = Solver(Params.channel(X, Y, **kw))
+    c = Solver(Params.channel(X, Y, flags=FLAG_NO_GRAPH, **kw))
+    monkeypatch.delenv("IBLB_FORM")
+    b = Solver(Params.channel(X, Y, flags=FLAG_NO_FUSE | FLAG_NO_GRAPH, **kw))
+    path = str(tmp_path / "f.ckp")
+    for n in (1, 2, 34):
+        for s in (a, b, c):
+            s.step(n)
+        ref = b.fields() + b.markers() + (b.force(), b.populations())
+        for s in (a, c):
+            got = s.fields() + s.markers() + (s.force(), s.populations())
+            for x, y in zip(ref, got):
+                assert np.array_equal(x, y)
+            assert s.Q == b.Q and s.it == b.it
+        if n == 2:
+            c.save_checkpoint(path)
+    # back to iteration 3 and forward again: the band's tiles start clean / flags start over
+    a.load_checkpoint(path)
+    a.step(34)
+    for x, y in zip(ref[0:2], a.fields()):
+        assert np.array_equal(x, y)
+    for s in (a, b, c):
+        s.close()
+
+
 def test_carpet_too_dense_for_the_tile_plans_falls_back_to_the_unfused_chain():
     """A carpet far denser than any reference script (16 cilia 12 columns apart: an 8-column tile
     can see more markers than a tile plan holds).  iblb_create bounds, from the per-marker envelopes
@@ -584,6 +622,32 @@ def test_carpet_too_dense_for_the_tile_plans_falls_back_to_the_unfused_chain():
         assert a.last_step_launches >= 3 * n
         for x, y in zip(a.fields() + a.markers() + (a.force(),), b.fields() + b.markers() + (b.force(),)):
             assert np.array_equal(x, y, equal_nan=True)
+    a.close()
+    b.close()
+
+
+@pytest.mark.parametrize("kw", [dict(c_num=6, c_fraction=6), dict(c_num=6, c_fraction=6, flags=FLAG_NO_FUSE),
+                                dict(c_num=6, c_fraction=6, flags=FLAG_NO_GRAPH)])
+def test_flux_history_gives_the_per_step_flux_without_per_step_syncs(kw):
+    """iblb_get_flux_history: Q after every iteration of a batch, bit-equal to stepping one
+    iteration at a time and reading Q each time (the reference's per-step copy, main.cu:928)."""
+    a = Solver(Params.channel(288, 192, **kw))
+    b = Solver(Params.channel(288, 192, **kw))
+    qs = []
+    for _ in range(75):
+        b.step(1)
+        qs.append(b.Q)
+    a.step(75)
+    assert np.array_equal(a.flux_history(0, 75), np.array(qs))
+    assert np.array_equal(a.flux_history(40, 10), np.array(qs[40:50]))
+    with pytest.raises(Exception, match="4096"):
+        a.flux_history(70, 10)
+    a.step(5000)  # the ring wraps
+    b.step(5000)
+    h = a.flux_history(5075 - 4096, 4096)
+    assert h[-1] == a.Q == b.Q and np.all(np.diff(h) != 0)
+    with pytest.raises(Exception, match="4096"):
+        a.flux_history(10, 5)
     a.close()
     b.close()
 

@@ -30,13 +30,13 @@ if __name__ == "__main__":
     for (X, Y, cn, cs, n) in cases:
         kw = dict(c_num=cn, c_space=cs, c_fraction=cn)
         # both single-launch forms (iblb_create picks one by the grid's wave count; IBLB_ROLES forces)
-        os.environ["IBLB_ROLES"] = "0"
-        t_tile = t_step(Params.channel(X, Y, **kw), n, 50)
-        os.environ["IBLB_ROLES"] = "1"
-        t_roles = t_step(Params.channel(X, Y, **kw), n, 50)
-        del os.environ["IBLB_ROLES"]
-        print("      single-launch forms: all-in-one tile CTA %.2f us, marker CTAs + LB CTAs %.2f us" % (
-            t_tile, t_roles), flush=True)
+        tf = []
+        for form in ("0", "1"):
+            os.environ["IBLB_FORM"] = form
+            tf.append(t_step(Params.channel(X, Y, **kw), n, 50))
+        del os.environ["IBLB_FORM"]
+        print("      forms of the iteration: all-in-one tile CTA %.2f us, marker CTAs + LB CTAs %.2f us" %
+              tuple(tf), flush=True)
         fused = t_step(Params.channel(X, Y, **kw), n, 50)
         fused_direct = t_step(Params.channel(X, Y, flags=FLAG_NO_GRAPH, **kw), n, 50)
         chain = t_step(Params.channel(X, Y, flags=FLAG_NO_FUSE, **kw), n, 50)
