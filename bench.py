@@ -442,14 +442,16 @@ def run_ours(a):
         e2e_value, h2d, d2h = None, 0, 0
 
     peak, peak_src = measured_peak()
-    # dominant kernel = lb_fused_v2: in the pure-LB workload the timed region is K launches of it
+    # dominant kernel = lb_fused_v4 (v2 on the 2G boundary columns of a slab): in the pure-LB workload
+    # the timed region is K launches of it
     lb_launches_per_rank = a.steps * (1 if n == 1 or WORKLOADS[a.workload]["scaling"] == "replicas" else 2)
     achieved = BYTES_PER_LUP * (nodes_total / n) * a.steps / t_dev / 1e9
     tr = ncu_traffic()
     # (whole channel with cilia on one GPU, short grid: the single-launch IB+LB kernel instead)
     w_ = WORKLOADS[a.workload]
     whole = n == 1 or w_["scaling"] == "replicas"
-    kernel = "lb_ib_tile_step" if (w_["c_num"] > 0 and whole and w_["Y"] <= 512) else "lb_fused_v2"
+    kernel = ("lb_ib_tile_step" if (w_["c_num"] > 0 and whole and w_["Y"] <= 512)
+              else "lb_fused_v4" if (w_["c_num"] == 0 and w_["Y"] % 128 == 0) else "lb_fused_v2")
     roof = {"bound": "hbm", "kernel": kernel, "achieved": round(achieved, 1),
             "peak": peak, "peak_source": peak_src, "unit": "GB/s",
             "frac": round(achieved / peak, 4),

@@ -313,7 +313,10 @@ __device__ __forceinline__ void list_spread(const TileMarkers &sh, const SpreadL
 // the per-thread hit masks of the spreading, and which nodes in and around the tile are support
 // nodes of the interpolation (ImmersedBoundary.cu:108-124) — the only ones whose moments the step
 // kernel has to form.
-__global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
+namespace {
+
+template <int MPC>
+__device__ __forceinline__ void tile_lists_body(const BandParams &p) {
     __shared__ short rel[kBandMaxRel];  // cilia whose bounding box overlaps the tile, ascending
     __shared__ int wcount[8];
     __shared__ int slist[kTileCap];
@@ -356,13 +359,14 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
     }
     __syncthreads();
     int n = 0;
-    for (int c0 = 0; c0 < nrel * p.mpc; c0 += 256) {
+    const int mpc = MPC ? MPC : p.mpc;
+    for (int c0 = 0; c0 < nrel * mpc; c0 += 256) {
         const int c = c0 + t;
         bool take = false;
         int k = 0;
-        if (c < nrel * p.mpc) {
-            const int q = c / p.mpc;
-            k = rel[q] * p.mpc + (c - q * p.mpc);
+        if (c < nrel * mpc) {
+            const int q = c / mpc;
+            k = rel[q] * mpc + (c - q * mpc);
             const float2 sm = ms[k];
             take = (meps[k] != 0) && sm.x >= xlo && sm.x <= xhi && sm.y >= ylo && sm.y <= yhi;
         }
@@ -396,12 +400,14 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
 #pragma unroll
     for (int w = 0; w < kHitWords; w++)
         pg.hit[w][t] = w * 32 < n ? hit_mask32(sbase, w * 32, n, tx0 + warp, ty0 + 2 * lane) : 0u;
-    {
+    // the support nodes: for lb_ib_tile_step the ring nodes + per-thread own flags, for
+    // lb_ib_roles_step all of them as cells of the moment table — only what the solver's form reads
+    int nring = 0, ncell = 0;
+    if (p.n_marker == 0) {
         const int c = (warp + 2) * kTabY + 2 * lane + 2;
         pg.own[t] = (unsigned char)((need[c] ? 1 : 0) | (need[c + 1] ? 2 : 0));
     }
-    int nring = 0;
-    const int nring_all = 4 * kTabY + 4 * tw;
+    const int nring_all = p.n_marker == 0 ? 4 * kTabY + 4 * tw : 0;
     for (int i0 = 0; i0 < nring_all; i0 += 256) {
         const int idx = i0 + t;
         const bool take = idx < nring_all && need[ring_cell(idx, tw)] != 0;
@@ -410,9 +416,7 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
         if (take) pg.ring[r] = (short)idx;
         nring += total;
     }
-    // the same support nodes, in the tile or around it, as cells of the moment table (role-split kernel)
-    int ncell = 0;
-    for (int i0 = 0; i0 < kTabCells; i0 += 256) {
+    for (int i0 = 0; i0 < (p.n_marker != 0 ? kTabCells : 0); i0 += 256) {
         const int idx = i0 + t;
         const bool take = idx < kTabCells && need[idx] != 0;
         int total;
@@ -426,6 +430,13 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
         pg.nring = nring;
         pg.ncell = ncell;
     }
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
+    if (p.mpc == kMarkersPerCilium) tile_lists_body<kMarkersPerCilium>(p);
+    else tile_lists_body<0>(p);
 }
 
 namespace {

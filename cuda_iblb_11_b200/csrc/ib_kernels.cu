@@ -47,14 +47,27 @@ __global__ void ib_coef(const int *k_of_j, float *coef, int mpc, int fine_points
 // Slot b of the marker arrays (stride Ns) receives iteration it0 + b.  Replaces the reference's
 // define_filament and boundary_check launches, off the fluid's critical path: one launch per
 // kKinBatch iterations.
-__global__ void __launch_bounds__(1024) ib_kinematics_batch(const IbParams p) {
-    __shared__ __align__(16) double trig[kMaxLeftCilia][24];  // slot 0 = own, e = cilium m-e
-    __shared__ float2 pos[kMaxLeftCilia][kMaxMarkersPerCilium];
-    __shared__ float2 vel[kMaxMarkersPerCilium];
-    __shared__ int closef[kMaxMarkersPerCilium];
-    __shared__ float wgt[kMaxMarkersPerCilium][8];
-    __shared__ float red_min[4], red_max[4];
-    const int mpc = p.mpc;  // markers per cilium, <= kMaxMarkersPerCilium
+// MPC: markers per cilium as a compile-time constant (the reference's 96: divisions by it fold
+// away — they cost 13 us per batch as run-time divisions), or 0 for the run-time value p.mpc.
+struct KinematicsShared {
+    __align__(16) double trig[kMaxLeftCilia][24];  // slot 0 = own, e = cilium m-e
+    float2 pos[kMaxLeftCilia * kMaxMarkersPerCilium];  // [e][j] with row pitch mpc: cilium m-e, marker j
+    float2 vel[kMaxMarkersPerCilium];
+    int closef[kMaxMarkersPerCilium];
+    float wgt[kMaxMarkersPerCilium][8];
+    float red_min[4], red_max[4];
+};
+
+template <int MPC>
+__device__ __forceinline__ void kinematics_body(const IbParams &p, KinematicsShared &sh) {
+    auto &trig = sh.trig;
+    auto &pos = sh.pos;
+    auto &vel = sh.vel;
+    auto &closef = sh.closef;
+    auto &wgt = sh.wgt;
+    auto &red_min = sh.red_min;
+    auto &red_max = sh.red_max;
+    const int mpc = MPC ? MPC : p.mpc;  // markers per cilium, <= kMaxMarkersPerCilium
     const int m = blockIdx.x, slot = blockIdx.y;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int it = (p.it_ptr ? *p.it_ptr : p.it) + p.it_off + slot;
@@ -80,7 +93,7 @@ __global__ void __launch_bounds__(1024) ib_kinematics_batch(const IbParams p) {
             sm = make_float2(r.x, r.y);
             v = make_float2(r.z, r.w);
         }
-        pos[e][j] = sm;
+        pos[idx] = sm;  // idx = e * mpc + j
         if (e == 0) vel[j] = v;
     }
     __syncthreads();
@@ -88,10 +101,10 @@ __global__ void __launch_bounds__(1024) ib_kinematics_batch(const IbParams p) {
     {
         const int j = t % mpc, part = t / mpc, nparts = 1024 / mpc;  // 10 scanners a marker at 96
         if (part < nparts) {
-            const float2 sm = pos[0][j];
+            const float2 sm = pos[j];
             bool close = false;
             for (int idx = part; idx < (r_max - 1) * mpc; idx += nparts) {
-                const float2 o = pos[1 + idx / mpc][idx % mpc];
+                const float2 o = pos[mpc + idx];
                 close |= (fabsf(o.x - sm.x) < 1) && (fabsf(o.y - sm.y) < 1);
             }
             if (close) closef[j] = 1;
@@ -100,7 +113,7 @@ __global__ void __launch_bounds__(1024) ib_kinematics_batch(const IbParams p) {
     // ---- spreading stencil: columns bx..bx+3, rows by..by+3 and their 1-D delta factors ----
     if (t < mpc * 8) {
         const int j = t >> 3, i = t & 7;
-        const float2 sm = pos[0][j];
+        const float2 sm = pos[j];
         const int bx = (int)ceilf(sm.x - 1.5f), by = (int)ceilf(sm.y - 1.5f);
         wgt[j][i] = (i < 4) ? delta_1d(fabsf((bx + i) - sm.x)) : delta_1d(fabsf((by + i - 4) - sm.y));
     }
@@ -108,7 +121,7 @@ __global__ void __launch_bounds__(1024) ib_kinematics_batch(const IbParams p) {
     if (t < mpc) {
         const long long k = (long long)slot * p.Ns + m * mpc + t;
         IBLB_CHK(slot >= 0 && slot < kKinBatch && m >= 0 && m < p.c_num);
-        const float2 sm = pos[0][t];
+        const float2 sm = pos[t];
         p.M.s[k] = sm;
         p.M.u_s[k] = vel[t];
         p.M.eps[k] = closef[t] ? 0 : 1;
@@ -118,7 +131,7 @@ __global__ void __launch_bounds__(1024) ib_kinematics_batch(const IbParams p) {
     }
     // bbox of the wrapped x positions (for the spreading tiles)
     if (t < 128) {
-        const float sx = (t < mpc) ? pos[0][t].x : 0.f;
+        const float sx = (t < mpc) ? pos[t].x : 0.f;
         float lo = (t < mpc) ? sx : 3.0e38f, hi = (t < mpc) ? sx : -3.0e38f;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -135,6 +148,12 @@ __global__ void __launch_bounds__(1024) ib_kinematics_batch(const IbParams p) {
         p.M.bbox[slot * p.c_num + m] =
             make_float2(fminf(fminf(red_min[0], red_min[1]), fminf(red_min[2], red_min[3])),
                         fmaxf(fmaxf(red_max[0], red_max[1]), fmaxf(red_max[2], red_max[3])));
+}
+
+__global__ void __launch_bounds__(1024, 2) ib_kinematics_batch(const IbParams p) {
+    __shared__ KinematicsShared sh;
+    if (p.mpc == kMarkersPerCilium) kinematics_body<kMarkersPerCilium>(p, sh);
+    else kinematics_body<0>(p, sh);
 }
 
 // F_s of every marker (ImmersedBoundary.cu:94-133), the only per-marker work that needs the fluid:

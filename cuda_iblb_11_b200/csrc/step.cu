@@ -35,7 +35,7 @@ BandParams make_band_params(const iblb_solver *s, int src_idx, int slot) {
     q.tile_flag = s->tile_flag;
     q.it_ptr = nullptr;
     q.it = (int)s->it;
-    q.n_marker = s->band_tiles * s->tiles_x;
+    q.n_marker = s->form == 1 ? s->band_tiles * s->tiles_x : 0;  // 0: lb_ib_tile_step's plan
     q.rows_lb = s->L.YDIM / 64;
     return q;
 }

@@ -1,9 +1,4 @@
 mkdir -p gpurun_out
-for n in 8 4; do
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2967$n bench.py --gpus $n --steps 100 --warmup 10 > gpurun_out/r02_bench_c2_n$n.json 2> gpurun_out/r02_bench_c2_n$n.err; echo "bench$n rc=$?"; cut -c1-400 gpurun_out/r02_bench_c2_n$n.json; python - <<PY
-import json
-d=json.load(open("gpurun_out/r02_bench_c2_n$n.json"))
-print("N=$n value", d["value"], "parity", d["parity"]["ok"], d["parity"]["c4s"].get("how"), d["parity"]["c4s"].get("bitwise_equal"), "c4", d["c4"].get("value"), d["c4"].get("ms_per_step"), "e2e", d["e2e"]["value"])
-PY
-done
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29699 tools/slab_ipc_check.py > gpurun_out/r02_slab_ipc_8.log 2>&1; echo "ipc rc=$?"; grep -E "case|IPC" gpurun_out/r02_slab_ipc_8.log
+python tools/ab_lib.py cuda_iblb_11_b200/libiblb_r2start.so cuda_iblb_11_b200/libiblb.so > gpurun_out/r02_ab_lib3.log 2>&1; cat gpurun_out/r02_ab_lib3.log
+timeout 900 python -m pytest tests -m gpu -q --timeout 600 > gpurun_out/r02_pytest_gpu_g.log 2>&1; echo "pytest rc=$?"; tail -n 6 gpurun_out/r02_pytest_gpu_g.log
+IBLB_TAG=r02g bash tools/gpu_sanitize.sh | tail -7
