@@ -582,8 +582,8 @@ __global__ void __launch_bounds__(256, 3) lb_ib_roles_step(const BandParams p) {
 // whole channel (ghost columns = its own opposite edge).  Row tiles >= band_rows/64 are plain LB;
 // on tall grids only the band tiles are launched here and lb_fused_v2 takes the rows above.
 // p.M and p.prog point at the iteration's slot.
-__global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];  // kTileSmemBytes, dynamic
+namespace {
+__device__ __forceinline__ void tile_step_body(const BandParams &p, unsigned char *smem_raw) {
     TileMarkers &sh = *reinterpret_cast<TileMarkers *>(smem_raw);
     SpreadLists &sl = *reinterpret_cast<SpreadLists *>(smem_raw + sizeof(TileMarkers));
     const LbParams &lp = p.lb;
@@ -711,6 +711,12 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
         for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
         if (lane == 0) flux_add(lp, tile_y, s / (double)L.YDIM);
     }
+}
+}  // namespace
+
+__global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];  // kTileSmemBytes, dynamic
+    tile_step_body(p, smem_raw);
 }
 
 // dynamic shared memory of lb_ib_tile_step (above the 48 KB static limit: opt-in per device)
