@@ -245,6 +245,16 @@ struct Channel {
 
 }  // namespace
 
+extern "C" int iblb_slab_range(int rank, int n_slabs, unsigned XDIM, unsigned align, unsigned *x0,
+                               unsigned *w) {
+    if (!x0 || !w || n_slabs < 1 || rank < 0 || rank >= n_slabs ||
+        !slab_range(rank, n_slabs, XDIM, align, *x0, *w)) {
+        iblb::set_error("iblb_slab_range: XDIM cannot be cut into that many slabs of whole `align` columns");
+        return IBLB_EINVAL;
+    }
+    return IBLB_OK;
+}
+
 extern "C" int iblb_run_gpus(const iblb_params *pp, const char *root, int n_gpus) {
     using namespace std;
     if (!pp) return IBLB_EINVAL;

@@ -108,7 +108,7 @@ SYMBOLS = [
     "iblb_last_step_launches", "iblb_profile_phases", "iblb_export_halo", "iblb_connect",
     "iblb_connect_local", "iblb_set_marker_replay", "iblb_run", "iblb_last_error", "iblb_version",
     "iblb_save_checkpoint", "iblb_load_checkpoint", "iblb_debug_violations", "iblb_run_gpus",
-    "iblb_device_count", "iblb_get_flux_history",
+    "iblb_device_count", "iblb_get_flux_history", "iblb_slab_range",
 ]
 
 

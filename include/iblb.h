@@ -184,6 +184,9 @@ int iblb_run(const iblb_params *p, const char *root);
  * file per slab (<path>.<slab>).  iblb_run takes n_gpus from the environment (IBLB_GPUS, default 1);
  * the reference is single-GPU (device selection: main.cu:395-396). */
 int iblb_run_gpus(const iblb_params *p, const char *root, int n_gpus);
+/* The partition iblb_run_gpus uses: columns [x0, x0+w) of slab `rank` of `n_slabs`, widths multiples
+ * of `align` (c_space with cilia, so that no cilium base sits on a seam), remainder to the low ranks. */
+int iblb_slab_range(int rank, int n_slabs, unsigned XDIM, unsigned align, unsigned *x0, unsigned *w);
 /* CUDA devices visible to this process (0 when the runtime cannot be initialised). */
 int iblb_device_count(void);
 

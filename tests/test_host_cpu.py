@@ -162,6 +162,23 @@ def test_sweep_script_parsing_and_assignment():
     assert slabs.assign_runs(6, 4) == [[0, 4], [1, 5], [2], [3]]
 
 
+def test_c_driver_partition_equals_the_python_one():
+    """iblb_slab_range (the x-slab partition of iblb_run_gpus / IBLB_GPUS) against
+    cuda_iblb_11_b200.slabs.slab_range, which bench.py and the IPC tests use."""
+    import ctypes
+    L = lib()
+    a, b = ctypes.c_uint(), ctypes.c_uint()
+    for X, n, align in ((32768, 8, 128), (288, 2, 48), (288, 4, 48), (576, 5, 48), (102, 4, 1),
+                        (8192, 3, 1), (4096, 8, 128)):
+        for r in range(n):
+            assert L.iblb_slab_range(r, n, X, align, ctypes.byref(a), ctypes.byref(b)) == 0
+            assert (a.value, b.value) == slabs.slab_range(r, n, X, align)
+    assert L.iblb_slab_range(0, 7, 288, 48, ctypes.byref(a), ctypes.byref(b)) != 0  # 6 units, 7 slabs
+    assert L.iblb_slab_range(0, 2, 100, 48, ctypes.byref(a), ctypes.byref(b)) != 0  # not whole units
+    with pytest.raises(ValueError):
+        slabs.slab_range(0, 7, 288, 48)
+
+
 def test_sweep_launcher_plan_names_and_summary(tmp_path, capsys):
     """cuda_iblb_11_b200.sweep: assignment of a script's lines to GPUs, flux-file names
     (main.cu:612), flux-curve reader and the summary table; no GPU involved."""
