@@ -523,10 +523,14 @@ __device__ __forceinline__ void lb_cta(const BandParams &p, int b) {
     const int tile = tile_y * p.tiles_x + tile_x;
     int n = 0;
     if (band_tile) n = __ldg(&p.prog[tile].n);
+    const bool active = x < L.W;  // warp-uniform: columns past the channel do nothing
+    // (offsets of this thread's vector loads: fluid-independent, formed before the wait)
+    const long long pcm = active ? L.off(x - 1, y0) : 0, pc0 = active ? L.off(x, y0) : 0,
+                    pcp = active ? L.off(x + 1, y0) : 0;
     pdl_wait();
-    if (x >= L.W) return;  // warp-uniform: columns past the channel
+    if (!active) return;
     Pulled q;
-    load_pulled(L, lp.src, x, y0, lane, q);
+    load_pulled_at(L, lp.src, pcm, pc0, pcp, y0, lane, q);
     double Fx0 = lp.gx, Fy0 = lp.gy, Fx1 = lp.gx, Fy1 = lp.gy;
     bool forced = (lp.gx != 0.0) | (lp.gy != 0.0);
     if (band_tile) forced = true;  // as the reference: spread's velocity update covers every node
@@ -641,20 +645,30 @@ __device__ __forceinline__ void tile_step_body(const BandParams &p, unsigned cha
         __syncthreads();  // the staged markers
         nlist = build_spread_list(sh, sl, n, x + L.x0, y0, hit);
     }
-    pdl_wait();
-    Pulled q;
-    if (active) load_pulled(L, lp.src, x, y0, lane, q);
-
-    // the support nodes in the two rings around the tile: the first 256 are pulled into registers
-    // now and turned into moments after this thread's own nodes, so that their latency overlaps
-    double rf[9] = {1., 0., 0., 0., 0., 0., 0., 0., 0.};
-    bool rvalid = false;
+    // (index arithmetic of this thread's ring node: still fluid-independent, still before the wait)
     int rc0 = 0;
+    long long ro[9];
+    bool rvalid = false;
     if (t < nring) {
         rc0 = ring_cell(r0, tw);
         const int lx = rc0 / kTabY, ly = rc0 - lx * kTabY;
-        rvalid = support_node_pull(L, lp.src, tx0 + L.x0 - 2 + lx, ty0 - 2 + ly, rf);
+        rvalid = support_node_offsets(L, tx0 + L.x0 - 2 + lx, ty0 - 2 + ly, ro);
     }
+    // ... and of this thread's own nine vector loads
+    const long long pcm = active ? L.off(x - 1, y0) : 0, pc0 = active ? L.off(x, y0) : 0,
+                    pcp = active ? L.off(x + 1, y0) : 0;
+    pdl_wait();
+    // The support nodes in the two rings around the tile: pulled into registers and turned into
+    // moments after this thread's own nodes.  Their (few, scattered) loads are issued BEFORE the
+    // tile's own 37 KB: behind those they queued for the whole load phase and the marker chain
+    // started ~2000 cycles late; in front of them they delay the bulk by a few hundred.
+    double rf[9] = {1., 0., 0., 0., 0., 0., 0., 0., 0.};
+    if (rvalid) {
+#pragma unroll
+        for (int i = 0; i < 9; i++) rf[i] = lp.src[ro[i]];
+    }
+    Pulled q;
+    if (active) load_pulled_at(L, lp.src, pcm, pc0, pcp, y0, lane, q);
     if (n > 0) {
         if (t + NT < nring) tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, ring_cell(r1, tw));
         if (!active) {  // columns past the channel (W % 8 != 0): as the reference would address them

@@ -108,8 +108,10 @@ __device__ __forceinline__ float delta_1d(float r) {
 // (0, y+1).  The node's nine populations are pulled out of the post-collision buffer `src` (pull
 // form of LatticeBoltzmann.cu:173-373 incl. the wall rules).  False when j lies outside the array
 // or the node's source columns are not held by this slab: such a node contributes nothing.
-__device__ __forceinline__ bool support_node_pull(const Lattice &L, const double *__restrict__ src,
-                                                  int x, int y, double (&f)[9]) {
+// (offsets first, loads second: lb_ib_tile_step forms the offsets before it waits for the previous
+// iteration — they do not depend on the fluid — and issues only the nine loads after)
+__device__ __forceinline__ bool support_node_offsets(const Lattice &L, int x, int y,
+                                                     long long (&o)[9]) {
     const long long j = (long long)y * L.XDIM + x;
     if (j < 0 || j >= (long long)L.XDIM * L.YDIM) return false;
     int ya = y, xa = x;
@@ -132,8 +134,17 @@ __device__ __forceinline__ bool support_node_pull(const Lattice &L, const double
             pi = (q == 4) ? 2 : (q == 7) ? 6 : 5;
             xsrc = xl; ysrc = ya;
         }
-        f[q] = src[pi * L.plane + L.off(xsrc, ysrc)];
+        o[q] = pi * L.plane + L.off(xsrc, ysrc);
     }
+    return true;
+}
+
+__device__ __forceinline__ bool support_node_pull(const Lattice &L, const double *__restrict__ src,
+                                                  int x, int y, double (&f)[9]) {
+    long long o[9];
+    if (!support_node_offsets(L, x, y, o)) return false;
+#pragma unroll
+    for (int q = 0; q < 9; q++) f[q] = src[o[q]];
     return true;
 }
 

@@ -124,10 +124,19 @@ struct Pulled {
     bool bot, top;  // lane 0 sits on the floor / lane 31 under the ceiling: e2 / e4 are v[4].x / v[2].y
 };
 
+__device__ __forceinline__ void load_pulled_at(const Lattice &L, const double *__restrict__ src,
+                                               long long cm, long long c0, long long cp, int y0,
+                                               int lane, Pulled &q);
 __device__ __forceinline__ void load_pulled(const Lattice &L, const double *__restrict__ src, int x,
                                             int y0, int lane, Pulled &q) {
+    load_pulled_at(L, src, L.off(x - 1, y0), L.off(x, y0), L.off(x + 1, y0), y0, lane, q);
+}
+// cm, c0, cp: offsets of (x-1, y0), (x, y0), (x+1, y0) within a population plane (a caller that has
+// to wait for the previous iteration forms them before it waits)
+__device__ __forceinline__ void load_pulled_at(const Lattice &L, const double *__restrict__ src,
+                                               long long cm, long long c0, long long cp, int y0,
+                                               int lane, Pulled &q) {
     const long long P = L.plane;
-    const long long cm = L.off(x - 1, y0), c0 = L.off(x, y0), cp = L.off(x + 1, y0);
     const bool at_bottom = (y0 == 0);
     const bool at_top = (y0 + 2 == L.YDIM);
     q.v[0] = ldg2(src + 0 * P + c0);

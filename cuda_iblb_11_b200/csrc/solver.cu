@@ -419,9 +419,9 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
             {
                 // Which single-launch form (bit-identical; measured in profiles/r02_time_small_*.log),
                 // by how many waves of all-in-one tile CTAs (two per SM) the grid would be:
-                //   up to 1.3 and beyond 4   lb_ib_tile_step: the tile's CTA does everything (the
+                //   up to 1.8 and beyond 4   lb_ib_tile_step: the tile's CTA does everything (the
                 //                            reference's own scripts are well under one wave);
-                //   1.3 .. 4                 lb_ib_roles_step: marker CTAs + light LB CTAs.
+                //   1.8 .. 4                 lb_ib_roles_step: marker CTAs + light LB CTAs.
                 // Tall grids (only the band's tiles in the IB kernel, the rest in lb_fused_v2/v4)
                 // keep the first.  IBLB_FORM=0/1 overrides (development).  A third form — ib_interp
                 // and a per-tile spreading kernel beside two LB launches on two streams — was
@@ -432,7 +432,7 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
                 const bool tall = L.YDIM / 64 > 8;
                 const int rows = tall ? s->band_tiles : L.YDIM / 64;
                 const double waves = (double)s->tiles_x * rows / (2. * sms);
-                s->form = (!tall && waves > 1.3 && waves <= 4.) ? 1 : 0;
+                s->form = (!tall && waves > 1.8 && waves <= 4.) ? 1 : 0;
                 if (const char *e = getenv("IBLB_FORM")) s->form = atoi(e) == 1 ? 1 : 0;
             }
             // Capacity of the per-tile plans, decided here and not at run time: an upper bound on
