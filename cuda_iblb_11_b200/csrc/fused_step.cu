@@ -582,7 +582,7 @@ __global__ void __launch_bounds__(256, 3) lb_ib_roles_step(const BandParams p) {
     else lb_cta(p, b - p.n_marker);
 }
 
-// grid = (row tiles, ceil(W/8)), block = 256.  Requires YDIM % 64 == 0 and a solver that owns the
+// grid = row tiles x column tiles (one dimension), block = 32*tw.  Requires YDIM % 64 == 0 and a solver that owns the
 // whole channel (ghost columns = its own opposite edge).  Row tiles >= band_rows/64 are plain LB;
 // on tall grids only the band tiles are launched here and lb_fused_v2 takes the rows above.
 // p.M and p.prog point at the iteration's slot.
@@ -592,7 +592,26 @@ __device__ __forceinline__ void tile_step_body(const BandParams &p, unsigned cha
     SpreadLists &sl = *reinterpret_cast<SpreadLists *>(smem_raw + sizeof(TileMarkers));
     const LbParams &lp = p.lb;
     const Lattice &L = lp.L;
-    const int tile_y = blockIdx.x, tile_x = blockIdx.y;
+    // Block index -> tile: the band's tiles first, the row tiles above the band last.  With
+    // programmatic dependent launch the next iteration's CTAs take the slots this iteration's CTAs
+    // free, in block-index order: the early slots (freed by tiles without markers) then go to band
+    // tiles, whose prologue (marker staging, spreading lists) runs under this iteration's tail; the
+    // last slots (freed by the slow marker tiles) go to tiles that have no prologue at all.
+    int tile_y, tile_x;
+    {
+        const int bt = min(p.rows_lb, p.band_rows >> 6), b = blockIdx.x, nb = bt * p.tiles_x;
+        if (!p.band_first) {  // grids that leave SMs empty: row tile fastest (measured faster there)
+            tile_x = b / p.rows_lb;
+            tile_y = b - tile_x * p.rows_lb;
+        } else if (b < nb) {
+            tile_x = b / bt;
+            tile_y = b - tile_x * bt;
+        } else {
+            const int r = b - nb, rt = p.rows_lb - bt;
+            tile_x = r / rt;
+            tile_y = bt + (r - tile_x * rt);
+        }
+    }
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int tw = p.tw, NT = tw * 32;  // columns per tile = warps of this CTA; threads
     const int tx0 = tile_x * tw, ty0 = tile_y * 64;

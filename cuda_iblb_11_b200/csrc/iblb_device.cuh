@@ -170,6 +170,7 @@ struct BandParams {
     int it;
     int n_marker;            // band row tiles x column tiles
     int rows_lb;             // row tiles the LB CTAs cover (all of them, or the band's on tall grids)
+    int band_first;          // lb_ib_tile_step: block order = the band's tiles, then the rows above
 };
 
 }  // namespace iblb

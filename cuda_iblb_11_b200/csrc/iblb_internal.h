@@ -77,6 +77,7 @@ struct iblb_solver {
     bool pdl_chain;            // the last kernel enqueued was lb_ib_tile_step over the whole grid
     iblb::TileProgram *prog;   // per slot and band tile: fluid-independent plan (ib_tile_lists)
     int form;                  // single-launch IB+LB iteration: 0 lb_ib_tile_step, 1 lb_ib_roles_step
+    int band_first;            // lb_ib_tile_step's block order (see fused_step.cu), chosen per grid
     int tile_w;                // columns per tile of lb_ib_tile_step: 8, or 6 where that fills the SMs better
     int tiles_x, band_tiles;   // column tiles, band row tiles
     int *tile_flag;            // per band tile: iteration + 1 whose force the band buffer holds

@@ -37,6 +37,7 @@ BandParams make_band_params(const iblb_solver *s, int src_idx, int slot) {
     q.it = (int)s->it;
     q.n_marker = s->form == 1 ? s->band_tiles * s->tiles_x : 0;  // 0: lb_ib_tile_step's plan
     q.rows_lb = s->L.YDIM / 64;
+    q.band_first = s->band_first;
     return q;
 }
 
@@ -197,7 +198,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         }
         // one CTA per tile (row tiles x column tiles), or marker CTAs followed by LB CTAs
         dim3 g = s->form == 1 ? dim3((unsigned)(bp.n_marker + bp.rows_lb * s->tiles_x))
-                          : dim3((unsigned)bp.rows_lb, (unsigned)s->tiles_x);
+                          : dim3((unsigned)(bp.rows_lb * s->tiles_x));
         // Programmatic dependent launch behind the previous iteration's lb_ib_tile_step: the
         // marker CTAs' fluid-independent prologue overlaps that kernel's tail.  Not right behind the
         // kernels that write what the prologue reads (kinematics, tile lists), and not on tall

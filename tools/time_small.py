@@ -34,9 +34,13 @@ if __name__ == "__main__":
         for form in ("0", "1"):
             os.environ["IBLB_FORM"] = form
             tf.append(t_step(Params.channel(X, Y, **kw), n, 50))
-        del os.environ["IBLB_FORM"]
-        print("      forms of the iteration: all-in-one tile CTA %.2f us, marker CTAs + LB CTAs %.2f us" %
-              tuple(tf), flush=True)
+        os.environ["IBLB_FORM"] = "0"
+        for bf in ("0", "1"):
+            os.environ["IBLB_BAND_FIRST"] = bf
+            tf.append(t_step(Params.channel(X, Y, **kw), n, 50))
+        del os.environ["IBLB_FORM"], os.environ["IBLB_BAND_FIRST"]
+        print("      forms of the iteration: all-in-one tile CTA %.2f us, marker CTAs + LB CTAs %.2f us; "
+              "tile CTA with row-fastest / band-first block order %.2f / %.2f us" % tuple(tf), flush=True)
         fused = t_step(Params.channel(X, Y, **kw), n, 50)
         fused_direct = t_step(Params.channel(X, Y, flags=FLAG_NO_GRAPH, **kw), n, 50)
         chain = t_step(Params.channel(X, Y, flags=FLAG_NO_FUSE, **kw), n, 50)
