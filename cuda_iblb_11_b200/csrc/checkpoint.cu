@@ -176,8 +176,6 @@ int iblb_load_checkpoint(iblb_solver *s, const char *path) {
     // completed iteration by the next getter (from the buffer that iteration pulled from)
     s->kin_base = -1;
     s->lists_base = -1;
-    if (s->tile_flag)  // iteration-numbered flags of the role-split step: the iteration may have gone back
-        IBLB_CUDA(cudaMemset(s->tile_flag, 0, sizeof(int) * (size_t)s->band_tiles * s->tiles_x));
     s->pdl_chain = false;
     s->ib_stale = s->p.c_num > 0 && it > 0;
     return IBLB_OK;

@@ -4,32 +4,23 @@
 //                                ib_tile_lists         per band tile and iteration: the ascending list of
 //                                                      markers whose 3x3 support can touch the tile
 //   every iteration              lb_ib_tile_step       F_s of the tile's markers -> spread -> pull-stream,
-//                                 (or lb_ib_roles_step) moments, TRT collide + Guo
+//                                                      moments, TRT collide + Guo
 //
 // Replaces the reference's interpolate, spread, streaming, macro, equilibrium, collision launches
 // (ImmersedBoundary.cu:94-267, LatticeBoltzmann.cu:30-411).  A tile is 8 (or 6) columns x 64 rows
 // (warp = column, lane = row pair).  Everything about the markers that does not depend on the fluid
 // — positions, velocities, epsilon, delta factors AND which markers reach which tile — is prescribed
 // (main.cu:77-252 is a function of `it` alone) and is computed off the fluid's critical path for a
-// batch of iterations.  What is left per iteration comes in two forms, same device functions, same
-// bits (tests/test_gpu_parity.py), chosen per grid by iblb_create:
-//
-// lb_ib_tile_step (grids of about one wave of CTAs: the reference's own scripts): the tile's CTA does
-//   everything.  It forms rho, u* of the support nodes it holds from the populations it pulls anyway
-//   and pulls those of the two rings around it, evaluates F_s of every marker on its list (nine
-//   support nodes each, ImmersedBoundary.cu:94-133; a marker that reaches two tiles is evaluated by
-//   both: no inter-CTA dependency, no atomics), then every node sums its spreading terms in
-//   ascending marker order (ImmersedBoundary.cu:178-203).  Neither F_s nor the force goes through
-//   global memory.  128 registers + 75 KB of shared memory: two CTAs per SM.
-//
-// lb_ib_roles_step (grids of several waves): two kinds of CTA in ONE grid.  Marker CTAs (the lowest
-//   block indices, one per band tile with markers) pull the support nodes, evaluate F_s, spread, store
-//   the tile's force in the band buffer and release the tile's flag with the iteration number; LB
-//   CTAs (every tile; lb_fused_v2's footprint, three per SM) issue their population loads, acquire
-//   the flag while those are in flight, read two force values per node pair, collide, store.  Lower
-//   block indices are dispatched first, so an LB CTA never waits for a marker CTA that is not
-//   resident; the spin is bounded all the same.  On one wave the extra L2 round trips (fence, flag,
-//   force) make it slower than the single-CTA form (profiles/r02_time_small_role_split.log).
+// batch of iterations.  What is left per iteration is done by the tile that needs it: a band
+// tile forms rho, u* of the support nodes it holds from the populations it pulls anyway and pulls
+// those of the two rings around it, evaluates F_s of every marker on its list (nine support nodes
+// each, ImmersedBoundary.cu:94-133; a marker that reaches two tiles is evaluated by both: no
+// inter-CTA dependency, no second launch, no atomics), then every node sums its spreading terms in
+// ascending marker order, the order of ImmersedBoundary.cu:178-203.  Neither F_s nor the force goes
+// through global memory: the force is consumed by the collision of the same thread.  Same device
+// functions as lb_fused_v2 / ib_interp / ib_spread: bit-identical results (tests/test_gpu_parity.py).
+// Two other forms of the iteration were built, measured and removed in round 2 (marker CTAs beside
+// light LB CTAs in one launch; marker kernels beside LB kernels on two streams): DESIGN.md section 3.
 #include "ib_device.cuh"
 #include "iblb_device.cuh"
 #include "lb_device.cuh"
@@ -353,7 +344,6 @@ __device__ __forceinline__ void tile_lists_body(const BandParams &p) {
             atomicExch(p.err, 1);
             pg.n = 0;
             pg.nring = 0;
-            pg.ncell = 0;
         }
         return;
     }
@@ -400,14 +390,13 @@ __device__ __forceinline__ void tile_lists_body(const BandParams &p) {
 #pragma unroll
     for (int w = 0; w < kHitWords; w++)
         pg.hit[w][t] = w * 32 < n ? hit_mask32(sbase, w * 32, n, tx0 + warp, ty0 + 2 * lane) : 0u;
-    // the support nodes: for lb_ib_tile_step the ring nodes + per-thread own flags, for
-    // lb_ib_roles_step all of them as cells of the moment table — only what the solver's form reads
-    int nring = 0, ncell = 0;
-    if (p.n_marker == 0) {
+    // the support nodes: per-thread flags for the tile's own nodes, a list for the ring nodes
+    int nring = 0;
+    {
         const int c = (warp + 2) * kTabY + 2 * lane + 2;
         pg.own[t] = (unsigned char)((need[c] ? 1 : 0) | (need[c + 1] ? 2 : 0));
     }
-    const int nring_all = p.n_marker == 0 ? 4 * kTabY + 4 * tw : 0;
+    const int nring_all = 4 * kTabY + 4 * tw;
     for (int i0 = 0; i0 < nring_all; i0 += 256) {
         const int idx = i0 + t;
         const bool take = idx < nring_all && need[ring_cell(idx, tw)] != 0;
@@ -416,19 +405,9 @@ __device__ __forceinline__ void tile_lists_body(const BandParams &p) {
         if (take) pg.ring[r] = (short)idx;
         nring += total;
     }
-    for (int i0 = 0; i0 < (p.n_marker != 0 ? kTabCells : 0); i0 += 256) {
-        const int idx = i0 + t;
-        const bool take = idx < kTabCells && need[idx] != 0;
-        int total;
-        const int r = ncell + cta_rank(take, wcount, total);
-        IBLB_CHK(!take || (r >= 0 && r < kTabCells));
-        if (take) pg.cells[r] = (short)idx;
-        ncell += total;
-    }
     if (t == 0) {
         pg.n = n;
         pg.nring = nring;
-        pg.ncell = ncell;
     }
 }
 
@@ -437,149 +416,6 @@ __device__ __forceinline__ void tile_lists_body(const BandParams &p) {
 __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
     if (p.mpc == kMarkersPerCilium) tile_lists_body<kMarkersPerCilium>(p);
     else tile_lists_body<0>(p);
-}
-
-namespace {
-
-__device__ __forceinline__ int ld_acquire_gpu(const int *p) {
-    int v;
-    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_gpu(int *p, int v) {
-    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-
-// Marker CTA of band tile `tile`: the tile's force of this iteration into the band buffer.
-__device__ __forceinline__ void marker_cta(const BandParams &p, unsigned char *smem_raw, int tile) {
-    TileMarkers &sh = *reinterpret_cast<TileMarkers *>(smem_raw);
-    SpreadLists &sl = *reinterpret_cast<SpreadLists *>(smem_raw + sizeof(TileMarkers));
-    const LbParams &lp = p.lb;
-    const Lattice &L = lp.L;
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const int tw = p.tw, NT = tw * 32;
-    const int tile_y = tile / p.tiles_x, tile_x = tile - tile_y * p.tiles_x;
-    const int tx0 = tile_x * tw, ty0 = tile_y * 64;
-    const int x = tx0 + warp, y0 = ty0 + 2 * lane;
-    const TileProgram *__restrict__ pg = p.prog + tile;
-    const int n = __ldg(&pg->n);
-    if (n == 0) return;  // nobody waits for a tile without markers
-    const int ncell = __ldg(&pg->ncell);
-    // ---- prologue: reads only the prescribed marker data (the tile's plan and its markers, written
-    // by kernels that completed before the first kernel of this PDL chain started), so it overlaps
-    // the tail of the previous iteration
-    unsigned hit[kHitWords] = {0u, 0u, 0u, 0u};
-#pragma unroll
-    for (int w = 0; w < kHitWords; w++)
-        if (w * 32 < n) hit[w] = __ldg(&pg->hit[w][t]);
-    const int c_first = t < ncell ? (int)__ldg(pg->cells + t) : 0;
-    for (int e = t; e < n; e += NT) {
-        const int k = __ldg(pg->list + e);
-        IBLB_CHK(k >= 0 && k < p.Ns && e < kTileCap);
-        const float2 sm = p.M.s[k], us = p.M.u_s[k];
-        const int2 b = p.M.base[k];
-        sh.su[e] = make_float4(sm.x, sm.y, us.x, us.y);
-        sh.fb[e] = make_float4(0.f, 0.f, __int_as_float(b.x), __int_as_float(b.y));
-        sh.wx[e] = p.M.wx[k];
-        sh.wy[e] = p.M.wy[k];
-    }
-    __syncthreads();  // the staged markers
-    const int nlist = build_spread_list(sh, sl, n, x + L.x0, y0, hit);
-    pdl_wait();  // the previous iteration has completed: its populations are visible
-    const int epoch = (p.it_ptr ? __ldcg(p.it_ptr) : 0) + p.it + 1;
-    // ---- rho, u* of the support nodes: one thread per node, nine independent pulls each
-    for (int i = t; i < ncell; i += NT)
-        tile_pulled_cell(L, lp.src, sh, tx0 + L.x0, ty0, i == t ? c_first : (int)__ldg(pg->cells + i));
-    __syncthreads();
-    for (int e = t; e < n; e += NT) tile_marker_force(sh, tx0 + L.x0, ty0, tw, e);
-    __syncthreads();
-    double fx0 = 0., fy0 = 0., fx1 = 0., fy1 = 0.;
-    list_spread(sh, sl, nlist, fx0, fy0, fx1, fy1);
-    tile_spread(sh, n, x + L.x0, y0, hit, fx0, fy0, fx1, fy1);  // what did not fit the list
-    if (x < L.W) {
-        IBLB_CHK(y0 >= 0 && y0 + 1 < lp.band_ld && tile >= 0 && tile < p.n_marker);
-        double *bp = p.band_w + (long long)x * lp.band_ld + y0;
-        __stcg(reinterpret_cast<double2 *>(bp), make_double2(fx0, fx1));
-        __stcg(reinterpret_cast<double2 *>(bp + (long long)L.W * lp.band_ld), make_double2(fy0, fy1));
-    }
-    __threadfence();
-    __syncthreads();
-    if (t == 0) st_release_gpu(p.tile_flag + tile, epoch);
-}
-
-// LB CTA of tile (tile_y, tile_x): lb_fused_v2's work on an 8x64 tile, plus — band tiles with
-// markers — the force the tile's marker CTA leaves in the band buffer.
-__device__ __forceinline__ void lb_cta(const BandParams &p, int b) {
-    const LbParams &lp = p.lb;
-    const Lattice &L = lp.L;
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    // rows above the band first: by the time the band's tiles are dispatched on a grid of several
-    // waves the marker CTAs have had a head start
-    const int ry = b / p.tiles_x, tile_x = b - ry * p.tiles_x;
-    const int tile_y = p.rows_lb - 1 - ry;
-    const int x = tile_x * p.tw + warp;
-    const int y0 = tile_y * 64 + 2 * lane;
-    const bool band_tile = tile_y * 64 < p.band_rows;  // block-uniform
-    const int tile = tile_y * p.tiles_x + tile_x;
-    int n = 0;
-    if (band_tile) n = __ldg(&p.prog[tile].n);
-    const bool active = x < L.W;  // warp-uniform: columns past the channel do nothing
-    // (offsets of this thread's vector loads: fluid-independent, formed before the wait)
-    const long long pcm = active ? L.off(x - 1, y0) : 0, pc0 = active ? L.off(x, y0) : 0,
-                    pcp = active ? L.off(x + 1, y0) : 0;
-    pdl_wait();
-    if (!active) return;
-    Pulled q;
-    load_pulled_at(L, lp.src, pcm, pc0, pcp, y0, lane, q);
-    double Fx0 = lp.gx, Fy0 = lp.gy, Fx1 = lp.gx, Fy1 = lp.gy;
-    bool forced = (lp.gx != 0.0) | (lp.gy != 0.0);
-    if (band_tile) forced = true;  // as the reference: spread's velocity update covers every node
-    if (n > 0) {
-        // the populations are on their way; meanwhile wait for the tile's force of THIS iteration
-        const int epoch = (p.it_ptr ? __ldcg(p.it_ptr) : 0) + p.it + 1;
-        if (lane == 0) {
-            const long long t0 = clock64();
-            while (ld_acquire_gpu(p.tile_flag + tile) < epoch) {
-                if (clock64() - t0 > (1ll << 32)) {  // ~2 s: never in a working launch
-                    atomicExch(p.err, 4);
-                    break;
-                }
-            }
-        }
-        __syncwarp();
-        IBLB_CHK(y0 >= 0 && y0 + 1 < lp.band_ld && tile >= 0 && tile < p.n_marker);
-        const double *bp = lp.band + (long long)x * lp.band_ld + y0;
-        const double2 bx = __ldcg(reinterpret_cast<const double2 *>(bp));
-        const double2 by = __ldcg(reinterpret_cast<const double2 *>(bp + (long long)L.W * lp.band_ld));
-        Fx0 += bx.x; Fx1 += bx.y; Fy0 += by.x; Fy1 += by.y;
-    }
-    double a[9], c[9];
-    shift_pulled(q, lane, a, c);
-    const double ux0 = collide_node(a, Fx0, Fy0, forced, lp);
-    const double ux1 = collide_node(c, Fx1, Fy1, forced, lp);
-    store_pair(lp, x, y0, a, c);
-    // flux through x = XDIM-5 (ImmersedBoundary.cu:259-264), same slots and order as lb_fused_v2
-    if (x == lp.xq && lp.qacc != nullptr) {
-        double s = ux0 + ux1;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
-        if (lane == 0) flux_add(lp, tile_y, s / (double)L.YDIM);
-    }
-}
-
-}  // namespace
-
-// grid = n_marker + rows_lb * tiles_x CTAs of 32*tw threads.  Requires YDIM % 64 == 0 and a solver
-// that owns the whole channel (ghost columns = its own opposite edge).  On tall grids rows_lb covers
-// the band only and lb_fused_v2 takes the rows above.  p.M and p.prog point at the iteration's slot.
-__global__ void __launch_bounds__(256, 3) lb_ib_roles_step(const BandParams p) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];  // marker CTAs only
-    // Programmatic dependent launch: the next iteration's CTAs may start as soon as every CTA of
-    // this one is running; each role calls pdl_wait() before it touches the populations.
-    pdl_launch_dependents();
-    const int b = blockIdx.x;
-    if (b < p.n_marker) marker_cta(p, smem_raw, b);
-    else lb_cta(p, b - p.n_marker);
 }
 
 // grid = row tiles x column tiles (one dimension), block = 32*tw.  Requires YDIM % 64 == 0 and a solver that owns the
@@ -755,10 +591,7 @@ __global__ void __launch_bounds__(256, 2) lb_ib_tile_step(const BandParams p) {
 // dynamic shared memory of lb_ib_tile_step (above the 48 KB static limit: opt-in per device)
 size_t tile_step_smem_bytes() { return sizeof(TileMarkers) + sizeof(SpreadLists); }
 cudaError_t tile_step_prepare() {
-    cudaError_t e = cudaFuncSetAttribute(lb_ib_tile_step, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)tile_step_smem_bytes());
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(lb_ib_roles_step, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    return cudaFuncSetAttribute(lb_ib_tile_step, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)tile_step_smem_bytes());
 }
 

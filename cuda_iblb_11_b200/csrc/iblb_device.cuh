@@ -143,13 +143,11 @@ constexpr int kRingNodes = 304;   // nodes of the two rings around an 8x64 tile 
 struct TileProgram {
     int n;                        // markers (epsilon != 0) whose 3x3 support can touch the tile
     int nring;                    // ring nodes that are support nodes of these markers
-    int ncell;                    // all support nodes, in the tile and in the rings
-    int pad;
+    int pad[2];
     int list[kTileCap];           // the markers' indices, ascending (the reference's summation order)
     unsigned hit[kHitWords][256]; // per thread (node pair): which of list[32w..32w+31] force its nodes
-    short ring[kRingNodes];       // lb_ib_tile_step: the needed ring nodes ...
-    unsigned char own[256];       // ... and per thread: bit 0/1 = node y0 / y0+1 is a support node
-    short cells[kTabCells];       // lb_ib_roles_step: all support nodes as cells of the moment table
+    short ring[kRingNodes];       // the needed ring nodes
+    unsigned char own[256];       // per thread: bit 0/1 = node y0 / y0+1 is a support node
 };
 static_assert(sizeof(TileProgram) % 16 == 0, "TileProgram alignment");
 
@@ -162,14 +160,7 @@ struct BandParams {
     int tiles_x;             // column tiles = ceil(W/tw)
     TileProgram *prog;       // [slot][band row tile][column tile]
     int *err;                // set non-zero when a tile exceeds kBandMaxRel / kTileCap
-    // lb_ib_roles_step only: the first n_marker CTAs evaluate the markers of one band tile each and
-    // leave the tile's force in the band buffer; the others are the LB tiles
-    double *band_w;          // the force band, written by the marker CTAs (lb.band reads it)
-    int *tile_flag;          // per band tile: (iteration + 1) whose force the band holds
-    const int *it_ptr;       // iteration = (it_ptr ? *it_ptr : 0) + it
-    int it;
-    int n_marker;            // band row tiles x column tiles
-    int rows_lb;             // row tiles the LB CTAs cover (all of them, or the band's on tall grids)
+    int rows_lb;             // row tiles the launch covers (all of them, or the band's on tall grids)
     int band_first;          // lb_ib_tile_step: block order = the band's tiles, then the rows above
 };
 

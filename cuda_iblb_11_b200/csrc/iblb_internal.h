@@ -35,7 +35,6 @@ __global__ void ib_interp(const IbParams p);
 __global__ void ib_spread(const IbParams p);
 __global__ void ib_tile_lists(const BandParams p);
 __global__ void lb_ib_tile_step(const BandParams p);
-__global__ void lb_ib_roles_step(const BandParams p);
 __global__ void it_advance(int *it_ptr, int by);
 unsigned long long checked_count_lb();     // IBLB_CHECKED builds: index violations per
 unsigned long long checked_count_ib();     // translation unit (0 in product builds)
@@ -76,11 +75,9 @@ struct iblb_solver {
     bool ib_stale;             // F_s / force band not materialised for the last step
     bool pdl_chain;            // the last kernel enqueued was lb_ib_tile_step over the whole grid
     iblb::TileProgram *prog;   // per slot and band tile: fluid-independent plan (ib_tile_lists)
-    int form;                  // single-launch IB+LB iteration: 0 lb_ib_tile_step, 1 lb_ib_roles_step
     int band_first;            // lb_ib_tile_step's block order (see fused_step.cu), chosen per grid
     int tile_w;                // columns per tile of lb_ib_tile_step: 8, or 6 where that fills the SMs better
     int tiles_x, band_tiles;   // column tiles, band row tiles
-    int *tile_flag;            // per band tile: iteration + 1 whose force the band buffer holds
     long long lists_base;      // tile lists hold iterations [lists_base, lists_base + kKinBatch); -1: none
     float reach_x, reach_y;    // bounds on the marker excursion from the cilium base
     std::vector<float> env;    // per marker of a cilium: x lo, x hi, y lo, y hi over the beat cycle

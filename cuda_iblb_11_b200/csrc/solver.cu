@@ -163,8 +163,6 @@ static int init_state(iblb_solver *s, const double *rho, const double *u) {
     if (s->band) IBLB_CUDA(cudaMemsetAsync(s->band, 0, sizeof(double) * 2 * s->L.W * s->band_ld, s->stream));
     IBLB_CUDA(cudaMemsetAsync(s->qacc, 0, sizeof(double) * s->nq, s->stream));
     if (s->it_dev) IBLB_CUDA(cudaMemsetAsync(s->it_dev, 0, sizeof(int), s->stream));
-    if (s->tile_flag)  // the tiles' force flags carry iteration numbers, which start over
-        IBLB_CUDA(cudaMemsetAsync(s->tile_flag, 0, sizeof(int) * (size_t)s->band_tiles * s->tiles_x, s->stream));
     s->cur = 0;
     s->ib_stale = false;
     s->kin_base = -1;
@@ -417,25 +415,13 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
             }
             s->tiles_x = (L.W + s->tile_w - 1) / s->tile_w;
             {
-                // Which single-launch form (bit-identical; measured in profiles/r02_time_small_*.log),
-                // by how many waves of all-in-one tile CTAs (two per SM) the grid would be:
-                //   up to 1.8 and beyond 4   lb_ib_tile_step: the tile's CTA does everything (the
-                //                            reference's own scripts are well under one wave);
-                //   1.8 .. 4                 lb_ib_roles_step: marker CTAs + light LB CTAs.
-                // Tall grids (only the band's tiles in the IB kernel, the rest in lb_fused_v2/v4)
-                // keep the first.  IBLB_FORM=0/1 overrides (development).  A third form — ib_interp
-                // and a per-tile spreading kernel beside two LB launches on two streams — was
-                // measured and dropped (profiles/r02_form2_dead_end.md).
+                // Block order of lb_ib_tile_step (fused_step.cu): band tiles first once the grid
+                // has more CTAs than SMs (C3: 7.4 -> 6.8 us, 1152x192: 13.0 -> 9.9 us), row tile
+                // fastest below, where SMs stay empty (C1: no difference to 5 %, box dependent).
                 cudaDeviceProp prop;
                 int sms = 148;
                 if (cudaGetDeviceProperties(&prop, s->device) == cudaSuccess) sms = prop.multiProcessorCount;
-                const bool tall = L.YDIM / 64 > 8;
-                const int rows = tall ? s->band_tiles : L.YDIM / 64;
-                const double waves = (double)s->tiles_x * rows / (2. * sms);
-                s->form = (!tall && waves > 1.8 && waves <= 4.) ? 1 : 0;
-                if (const char *e = getenv("IBLB_FORM")) s->form = atoi(e) == 1 ? 1 : 0;
-                // block order of lb_ib_tile_step: band tiles first once the grid has more CTAs than
-                // SMs (C3: 7.05 -> 6.8 us), row tile fastest below (C1: 5.58 vs 5.84 us)
+                const int rows = (L.YDIM / 64 > 8) ? s->band_tiles : L.YDIM / 64;
                 s->band_first = (long long)s->tiles_x * rows > sms ? 1 : 0;
                 if (const char *e = getenv("IBLB_BAND_FIRST")) s->band_first = atoi(e) != 0;
             }
@@ -474,9 +460,6 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
             cudaError_t e = tile_step_prepare();
             if (e == cudaSuccess) e = cudaMalloc((void **)&s->prog, sizeof(TileProgram) * nt);
             if (e == cudaSuccess) e = cudaMemset(s->prog, 0, sizeof(TileProgram) * nt);
-            const size_t nf = sizeof(int) * (size_t)s->band_tiles * s->tiles_x;
-            if (e == cudaSuccess) e = cudaMalloc((void **)&s->tile_flag, nf);
-            if (e == cudaSuccess) e = cudaMemset(s->tile_flag, 0, nf);
             if (e != cudaSuccess) {
                 iblb_destroy(s);
                 return cuda_fail(e, "cudaMalloc(tile lists)");
@@ -524,7 +507,6 @@ int iblb_destroy(iblb_solver *s) {
     cudaFree(s->M.wx); cudaFree(s->M.wy); cudaFree(s->M.base);
     cudaFree(s->k_of_j_dev); cudaFree(s->it_dev);
     cudaFree(s->prog);
-    cudaFree(s->tile_flag);
     cudaFree(s->replay_dev);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);

@@ -31,11 +31,6 @@ BandParams make_band_params(const iblb_solver *s, int src_idx, int slot) {
     q.tiles_x = s->tiles_x;
     q.prog = s->prog + (size_t)slot * s->band_tiles * s->tiles_x;
     q.err = s->err_dev;
-    q.band_w = s->band;
-    q.tile_flag = s->tile_flag;
-    q.it_ptr = nullptr;
-    q.it = (int)s->it;
-    q.n_marker = s->form == 1 ? s->band_tiles * s->tiles_x : 0;  // 0: lb_ib_tile_step's plan
     q.rows_lb = s->L.YDIM / 64;
     q.band_first = s->band_first;
     return q;
@@ -192,13 +187,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         // lb_fused_v2
         const bool split = tiles_y > 8;
         bp.rows_lb = split ? band_tiles : tiles_y;
-        if (graph_mode) {  // the iteration number lives on the device (see build_graph)
-            bp.it_ptr = s->it_dev;
-            bp.it = graph_it_off;
-        }
-        // one CTA per tile (row tiles x column tiles), or marker CTAs followed by LB CTAs
-        dim3 g = s->form == 1 ? dim3((unsigned)(bp.n_marker + bp.rows_lb * s->tiles_x))
-                          : dim3((unsigned)(bp.rows_lb * s->tiles_x));
+        dim3 g((unsigned)(bp.rows_lb * s->tiles_x));  // one CTA per tile
         // Programmatic dependent launch behind the previous iteration's lb_ib_tile_step: the
         // marker CTAs' fluid-independent prologue overlaps that kernel's tail.  Not right behind the
         // kernels that write what the prologue reads (kinematics, tile lists), and not on tall
@@ -215,8 +204,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         const bool pdl = !split && !fresh_plan && chain && !(s->p.flags & IBLB_FLAG_NO_PDL);
         cfg.attrs = &attr;
         cfg.numAttrs = pdl ? 1 : 0;
-        if (s->form == 1) IBLB_CUDA(cudaLaunchKernelEx(&cfg, lb_ib_roles_step, bp));
-        else IBLB_CUDA(cudaLaunchKernelEx(&cfg, lb_ib_tile_step, bp));
+        IBLB_CUDA(cudaLaunchKernelEx(&cfg, lb_ib_tile_step, bp));
         s->pdl_chain = !split;
         launches += 1;
         if (split) {

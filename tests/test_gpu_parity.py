@@ -569,22 +569,22 @@ def test_tall_grid_split_step_equals_separate_kernels_and_oracle(c_num, c_space,
     o.close()
 
 
-@pytest.mark.parametrize("form", ["0", "1"])
+@pytest.mark.parametrize("form", ["0", "1"])  # IBLB_BAND_FIRST
 @pytest.mark.parametrize("c_num,c_space,c_fraction,Y", [
     (6, 48, 6, 192), (12, 48, 5, 192), (5, 44, 5, 192), (16, 128, 16, 128), (48, 48, 48, 192),
 ])
-def test_every_form_of_the_iteration_is_bit_identical(form, c_num, c_space, c_fraction, Y,
+def test_both_block_orders_of_the_iteration_are_bit_identical(form, c_num, c_space, c_fraction, Y,
                                                       monkeypatch, tmp_path):
-    """iblb_create picks one of two forms of the single-launch IB+LB iteration by the size of the
-    grid (all-in-one tile CTA / marker CTAs + LB CTAs); IBLB_FORM forces each of them here, on small and wide grids, with
+    """iblb_create picks the block order of the single-launch IB+LB iteration by the size of the
+    grid (row tile fastest / the band's tiles first); IBLB_BAND_FIRST forces each of them here, on small and wide grids, with
     CUDA-graph batches and with direct launches, through a checkpoint and back: always the state of
     the unfused chain, bit for bit."""
     X = c_num * c_space
     kw = dict(c_num=c_num, c_space=c_space, c_fraction=c_fraction)
-    monkeypatch.setenv("IBLB_FORM", form)
+    monkeypatch.setenv("IBLB_BAND_FIRST", form)
     a = Solver(Params.channel(X, Y, **kw))
     c = Solver(Params.channel(X, Y, flags=FLAG_NO_GRAPH, **kw))
-    monkeypatch.delenv("IBLB_FORM")
+    monkeypatch.delenv("IBLB_BAND_FIRST")
     b = Solver(Params.channel(X, Y, flags=FLAG_NO_FUSE | FLAG_NO_GRAPH, **kw))
     path = str(tmp_path / "f.ckp")
     for n in (1, 2, 34):
@@ -598,7 +598,7 @@ def test_every_form_of_the_iteration_is_bit_identical(form, c_num, c_space, c_fr
             assert s.Q == b.Q and s.it == b.it
         if n == 2:
             c.save_checkpoint(path)
-    # back to iteration 3 and forward again: the band's tiles start clean / flags start over
+    # back to iteration 3 and forward again
     a.load_checkpoint(path)
     a.step(34)
     for x, y in zip(ref[0:2], a.fields()):

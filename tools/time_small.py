@@ -29,18 +29,14 @@ if __name__ == "__main__":
         cases = cases[:int(sys.argv[1])]
     for (X, Y, cn, cs, n) in cases:
         kw = dict(c_num=cn, c_space=cs, c_fraction=cn)
-        # both single-launch forms (iblb_create picks one by the grid's wave count; IBLB_ROLES forces)
+        # both block orders (iblb_create picks one by the grid's size; IBLB_BAND_FIRST forces)
         tf = []
-        for form in ("0", "1"):
-            os.environ["IBLB_FORM"] = form
-            tf.append(t_step(Params.channel(X, Y, **kw), n, 50))
-        os.environ["IBLB_FORM"] = "0"
         for bf in ("0", "1"):
             os.environ["IBLB_BAND_FIRST"] = bf
             tf.append(t_step(Params.channel(X, Y, **kw), n, 50))
-        del os.environ["IBLB_FORM"], os.environ["IBLB_BAND_FIRST"]
-        print("      forms of the iteration: all-in-one tile CTA %.2f us, marker CTAs + LB CTAs %.2f us; "
-              "tile CTA with row-fastest / band-first block order %.2f / %.2f us" % tuple(tf), flush=True)
+        del os.environ["IBLB_BAND_FIRST"]
+        print("      block order of lb_ib_tile_step: row tile fastest %.2f us, band tiles first %.2f us" %
+              tuple(tf), flush=True)
         fused = t_step(Params.channel(X, Y, **kw), n, 50)
         fused_direct = t_step(Params.channel(X, Y, flags=FLAG_NO_GRAPH, **kw), n, 50)
         chain = t_step(Params.channel(X, Y, flags=FLAG_NO_FUSE, **kw), n, 50)
