@@ -119,6 +119,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
     const bool chain = s->pdl_chain;  // the previous kernel in the stream is lb_ib_tile_step
     s->pdl_chain = false;
     bool fresh_plan = false;          // this iteration launched what the fused prologue reads
+    bool ib_pending = false;          // two streams: spreading of this iteration recorded in ev_ib
     int slot = 0;
     if (s->p.c_num > 0) {
         // marker kinematics, epsilon, spreading stencils: a batch of kKinBatch iterations at once
@@ -169,9 +170,9 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
             launches += 1;
             IBLB_CUDA(cudaGetLastError());
             s->ib_stale = false;
-            if (two) {  // the interior kernel reads the force band
+            if (two) {  // the interior kernel's band rows read the force band (waited for below)
                 IBLB_CUDA(cudaEventRecord(s->ev_ib, sb));
-                IBLB_CUDA(cudaStreamWaitEvent(st, s->ev_ib, 0));
+                ib_pending = true;
             }
         }
     } else if (pe) {
@@ -236,6 +237,18 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
         qi.col_count = W - 2 * G;
         qi.left.G = 0;
         qi.right.G = 0;
+        if (ib_pending && s->vec2 && s->band_rows < s->L.YDIM) {
+            // the rows above the force band need nothing from the markers: they start at once
+            // (four nodes per thread where the row count allows), beside interpolation and spreading
+            // on the boundary stream; the band's rows follow the spreading
+            LbParams qt = qi;
+            qt.band = nullptr;
+            qt.row_begin = s->band_rows;
+            rc = launch_lb(s, qt, st, launches);
+            if (rc) return rc;
+            qi.row_end = s->band_rows;
+        }
+        if (ib_pending) IBLB_CUDA(cudaStreamWaitEvent(st, s->ev_ib, 0));
         rc = launch_lb(s, qi, st, launches);
         if (rc) return rc;
         if (two) IBLB_CUDA(cudaEventRecord(s->ev_i, st));
