@@ -1,10 +1,5 @@
 mkdir -p gpurun_out
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29655 tools/slab_ipc_check.py > gpurun_out/r02_slab_ipc_2b.log 2>&1; echo "ipc rc=$?"; grep -E "case|IPC" gpurun_out/r02_slab_ipc_2b.log
-timeout 900 python -m pytest tests/test_gpu_slabs_fullsize.py -m gpu -q --timeout 600 -k "slabs or gpus" > gpurun_out/r02_pytest_2gpu_b.log 2>&1; echo "pytest rc=$?"; tail -n 4 gpurun_out/r02_pytest_2gpu_b.log
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29656 bench.py --gpus 2 --steps 100 --warmup 10 > gpurun_out/r02_bench_c2_n2b.json 2> gpurun_out/r02_bench_c2_n2b.err; echo "bench2 rc=$?"
-python - <<PY
-import json
-for line in open("gpurun_out/r02_bench_c2_n2b.json"):
-    if line.startswith("{"):
-        d=json.loads(line); print(d["value"], d["ms_per_step"], d["parity"]["ok"], d["parity"]["c4s"].get("bitwise_equal"), d["c4"])
-PY
+for n in 8 4; do
+rm -rf /tmp/D$n; s=$(date +%s.%N); IBLB_ROOT=/tmp/D$n IBLB_GPUS=$n IBLB_YDIM=32768 IBLB_ITERATIONS=201 ./app 256 256 128 1.0 1.0 5 1.0 100 0 0 > gpurun_out/r02_app_c4_gpus$n.log 2>&1; echo "app$n rc=$? wall $(echo "$(date +%s.%N) - $s" | bc) s"; tail -n 3 gpurun_out/r02_app_c4_gpus$n.log; tail -n 4 /tmp/D$n/Raw/256/256/SimLog.txt; tail -n 2 /tmp/D$n/Flux/*-flux.dat; cp /tmp/D$n/Raw/256/256/SimLog.txt gpurun_out/r02_app_c4_gpus${n}_SimLog.txt
+done
+cmp /tmp/D8/Flux/256_256_128_1_1x5-flux.dat /tmp/D4/Flux/256_256_128_1_1x5-flux.dat && echo "flux files identical (8 vs 4 slabs)"
