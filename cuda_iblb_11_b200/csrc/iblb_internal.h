@@ -111,7 +111,6 @@ struct iblb_solver {
     int *nb_rel[2];            // left neighbour's flags[3], right neighbour's flags[2] (release)
     cudaStream_t stream_b;     // coupled slabs: wait -> boundary columns -> signal run here,
     cudaEvent_t ev_b, ev_i, ev_ib;  // beside the interior kernel on `stream` (events order them)
-    bool two_stream_primed;    // ev_b / ev_i have been recorded at least once
     long long slab_timeout_ns; // bound on slab_wait's spin (IBLB_SLAB_TIMEOUT_S, default 60 s)
     void *nb_flag_mapped[2];
     bool self_left, self_right;
