@@ -422,6 +422,24 @@ __global__ void __launch_bounds__(256) ib_tile_lists(const BandParams p) {
 // whole channel (ghost columns = its own opposite edge).  Row tiles >= band_rows/64 are plain LB;
 // on tall grids only the band tiles are launched here and lb_fused_v2 takes the rows above.
 // p.M and p.prog point at the iteration's slot.
+// Development build (-DIBLB_TILE_TIMING, tools/tile_timing.sh): thread 0 of every CTA stamps clock64()
+// at the phase boundaries of lb_ib_tile_step into p.dbg[cta][16] (slot 13: latest exit over all
+// threads, 14 / 15: markers / ring nodes of the tile); iblb_destroy prints the averages.
+#ifdef IBLB_TILE_TIMING
+#define TSTAMP(i)                                                                     \
+    do {                                                                              \
+        if (threadIdx.x == 0 && p.dbg) p.dbg[(long long)blockIdx.x * 16 + (i)] = clock64(); \
+    } while (0)
+#define TSTAMP_EXIT()                                                                                  \
+    do {                                                                                               \
+        if (p.dbg) atomicMax((unsigned long long *)&p.dbg[(long long)blockIdx.x * 16 + 13],           \
+                             (unsigned long long)clock64());                                           \
+    } while (0)
+#else
+#define TSTAMP(i)
+#define TSTAMP_EXIT()
+#endif
+
 namespace {
 __device__ __forceinline__ void tile_step_body(const BandParams &p, unsigned char *smem_raw) {
     TileMarkers &sh = *reinterpret_cast<TileMarkers *>(smem_raw);
@@ -462,6 +480,10 @@ __device__ __forceinline__ void tile_step_body(const BandParams &p, unsigned cha
     // PDL chain started), so it overlaps the tail of the previous iteration; pdl_wait() returns once
     // the previous iteration has completed and its populations are visible.
     pdl_launch_dependents();
+    TSTAMP(0);
+#ifdef IBLB_TILE_TIMING
+    if (threadIdx.x == 0 && p.dbg) p.dbg[(long long)blockIdx.x * 16 + 13] = 0;
+#endif
     int n = 0, nring = 0;
     const TileProgram *__restrict__ pg = nullptr;
     if (band_tile) {
@@ -512,7 +534,15 @@ __device__ __forceinline__ void tile_step_body(const BandParams &p, unsigned cha
     // ... and of this thread's own nine vector loads
     const long long pcm = active ? L.off(x - 1, y0) : 0, pc0 = active ? L.off(x, y0) : 0,
                     pcp = active ? L.off(x + 1, y0) : 0;
+    TSTAMP(1);
     pdl_wait();
+    TSTAMP(2);
+#ifdef IBLB_TILE_TIMING
+    if (threadIdx.x == 0 && p.dbg) {
+        p.dbg[(long long)blockIdx.x * 16 + 14] = n;
+        p.dbg[(long long)blockIdx.x * 16 + 15] = nring;
+    }
+#endif
     // The support nodes in the two rings around the tile: pulled into registers and turned into
     // moments after this thread's own nodes.  Their (few, scattered) loads are issued BEFORE the
     // tile's own 37 KB: behind those they queued for the whole load phase and the marker chain
@@ -533,8 +563,21 @@ __device__ __forceinline__ void tile_step_body(const BandParams &p, unsigned cha
         }
     }
 
+    TSTAMP(3);
+    // the ring nodes' moments now, while the tile's own loads are still in flight (the ring pulls
+    // were issued first and are back first)
+    if (n > 0 && t < nring) {
+        double rho, ux, uy;
+        node_moments(rf, rho, ux, uy);  // rf = (1, 0, ...) placeholder when !rvalid
+        sh.rho[rc0] = rvalid ? rho : 0.;
+        sh.ux[rc0] = rvalid ? ux : 0.;
+        sh.uy[rc0] = rvalid ? uy : 0.;
+    }
+
+    TSTAMP(4);
     double a[9], b[9];
     if (active) shift_pulled(q, lane, a, b);
+    TSTAMP(5);
 
     double Fx0 = lp.gx, Fy0 = lp.gy, Fx1 = lp.gx, Fy1 = lp.gy;
     bool forced = (lp.gx != 0.0) | (lp.gy != 0.0);
@@ -552,26 +595,27 @@ __device__ __forceinline__ void tile_step_body(const BandParams &p, unsigned cha
                 sh.rho[c + 1] = r1_; sh.ux[c + 1] = x1_; sh.uy[c + 1] = y1_;
             }
         }
-        if (t < nring) {
-            double rho, ux, uy;
-            node_moments(rf, rho, ux, uy);  // rf = (1, 0, ...) placeholder when !rvalid
-            sh.rho[rc0] = rvalid ? rho : 0.;
-            sh.ux[rc0] = rvalid ? ux : 0.;
-            sh.uy[rc0] = rvalid ? uy : 0.;
-        }
+        TSTAMP(6);
         __syncthreads();
+        TSTAMP(7);
         if (t < n) tile_marker_force(sh, tx0 + L.x0, ty0, tw, t);
         if (t + NT < n) tile_marker_force(sh, tx0 + L.x0, ty0, tw, t + NT);
+        TSTAMP(8);
         __syncthreads();
+        TSTAMP(9);
         double fx0 = 0., fy0 = 0., fx1 = 0., fy1 = 0.;
         list_spread(sh, sl, nlist, fx0, fy0, fx1, fy1);
         tile_spread(sh, n, x + L.x0, y0, hit, fx0, fy0, fx1, fy1);  // what did not fit the list
         Fx0 += fx0; Fy0 += fy0; Fx1 += fx1; Fy1 += fy1;
+        TSTAMP(10);
     }
     if (!active) return;
     const double ux0 = collide_node(a, Fx0, Fy0, forced, lp);
     const double ux1 = collide_node(b, Fx1, Fy1, forced, lp);
+    TSTAMP(11);
     store_pair(lp, x, y0, a, b);
+    TSTAMP(12);
+    TSTAMP_EXIT();
 
     // flux through x = XDIM-5 (ImmersedBoundary.cu:259-264), same slots and order as lb_fused_v2
     if (x == lp.xq && lp.qacc != nullptr) {

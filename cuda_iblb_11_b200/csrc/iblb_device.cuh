@@ -160,6 +160,9 @@ struct BandParams {
     int tiles_x;             // column tiles = ceil(W/tw)
     TileProgram *prog;       // [slot][band row tile][column tile]
     int *err;                // set non-zero when a tile exceeds kBandMaxRel / kTileCap
+#ifdef IBLB_TILE_TIMING
+    long long *dbg;          // development: clock64 stamps of lb_ib_tile_step, 16 per CTA
+#endif
     int rows_lb;             // row tiles the launch covers (all of them, or the band's on tall grids)
     int band_first;          // lb_ib_tile_step: block order = the band's tiles, then the rows above
 };

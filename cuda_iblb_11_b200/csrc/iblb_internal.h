@@ -83,6 +83,9 @@ struct iblb_solver {
     std::vector<float> env;    // per marker of a cilium: x lo, x hi, y lo, y hi over the beat cycle
     int tile_bound;            // upper bound on the markers that can ever touch one tile
     int *err_dev;
+#ifdef IBLB_TILE_TIMING
+    long long *dbg_dev;        // development: phase stamps of lb_ib_tile_step
+#endif
     float4 *replay_dev;        // iblb_set_marker_replay (test hook) or null
     int replay_steps, replay_j;
     // flux

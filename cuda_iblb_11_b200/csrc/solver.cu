@@ -460,6 +460,11 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
             cudaError_t e = tile_step_prepare();
             if (e == cudaSuccess) e = cudaMalloc((void **)&s->prog, sizeof(TileProgram) * nt);
             if (e == cudaSuccess) e = cudaMemset(s->prog, 0, sizeof(TileProgram) * nt);
+#ifdef IBLB_TILE_TIMING
+            const size_t nd = (size_t)(L.YDIM / 64) * s->tiles_x * 16;
+            if (e == cudaSuccess) e = cudaMalloc((void **)&s->dbg_dev, sizeof(long long) * nd);
+            if (e == cudaSuccess) e = cudaMemset(s->dbg_dev, 0, sizeof(long long) * nd);
+#endif
             if (e != cudaSuccess) {
                 iblb_destroy(s);
                 return cuda_fail(e, "cudaMalloc(tile lists)");
@@ -492,6 +497,41 @@ int iblb_destroy(iblb_solver *s) {
     if (!s) return IBLB_OK;
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
+#ifdef IBLB_TILE_TIMING
+    if (s->dbg_dev) {  // phase stamps of the LAST lb_ib_tile_step launch, per CTA (tools/tile_timing.sh)
+        const int ty = s->L.YDIM / 64 > 8 ? s->band_tiles : s->L.YDIM / 64;
+        const size_t nc = (size_t)ty * s->tiles_x;
+        std::vector<long long> h(nc * 16);
+        cudaMemcpy(h.data(), s->dbg_dev, sizeof(long long) * nc * 16, cudaMemcpyDeviceToHost);
+        static const char *name[13] = {"entry", "prologue done", "wait returned", "loads issued",
+                                       "ring moments", "bulk arrived+shift", "own moments",
+                                       "barrier 1", "F_s", "barrier 2", "spread", "collide", "stores issued"};
+        for (int cls = 0; cls < 3; cls++) {  // tiles without markers / with markers / the 10 % with most
+            std::vector<size_t> sel;
+            long long nmax = 0;
+            for (size_t c = 0; c < nc; c++) nmax = std::max(nmax, h[c * 16 + 14]);
+            for (size_t c = 0; c < nc; c++) {
+                const long long n = h[c * 16 + 14];
+                if ((cls == 0 && n == 0) || (cls == 1 && n > 0) || (cls == 2 && n > 0 && n * 10 >= nmax * 7))
+                    sel.push_back(c);
+            }
+            if (sel.empty()) continue;
+            fprintf(stderr, "tile timing, %zu CTAs %s, cycles after the wait returned (thread 0), avg:\n",
+                    sel.size(), cls == 0 ? "without markers" : cls == 1 ? "with markers" : "with >= 70 % of the most markers");
+            for (int i = 0; i < 13; i++) {
+                double a = 0;
+                int cnt = 0;
+                for (size_t c : sel)
+                    if (h[c * 16 + i] != 0) { a += (double)(h[c * 16 + i] - h[c * 16 + 2]); cnt++; }
+                if (cnt) fprintf(stderr, "  %-20s %9.0f  (%d CTAs)\n", name[i], a / cnt, cnt);
+            }
+            double ex = 0, nn = 0, nr = 0;
+            for (size_t c : sel) { ex += (double)(h[c * 16 + 13] - h[c * 16 + 2]); nn += h[c * 16 + 14]; nr += h[c * 16 + 15]; }
+            fprintf(stderr, "  %-20s %9.0f   markers avg %.1f, ring nodes avg %.1f\n", "last thread exit", ex / sel.size(), nn / sel.size(), nr / sel.size());
+        }
+        cudaFree(s->dbg_dev);
+    }
+#endif
     if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
     cudaFree(s->err_dev);
     for (int f = 0; f < 2; f++) {

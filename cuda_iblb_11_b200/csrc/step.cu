@@ -31,6 +31,9 @@ BandParams make_band_params(const iblb_solver *s, int src_idx, int slot) {
     q.tiles_x = s->tiles_x;
     q.prog = s->prog + (size_t)slot * s->band_tiles * s->tiles_x;
     q.err = s->err_dev;
+#ifdef IBLB_TILE_TIMING
+    q.dbg = s->dbg_dev;
+#endif
     q.rows_lb = s->L.YDIM / 64;
     q.band_first = s->band_first;
     return q;
