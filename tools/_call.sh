@@ -1,3 +1,11 @@
 mkdir -p gpurun_out
-python tools/ab_lib.py cuda_iblb_11_b200/libiblb_before.so cuda_iblb_11_b200/libiblb.so > gpurun_out/r02_ab_y.log 2>&1; cat gpurun_out/r02_ab_y.log
-timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -q --timeout 600 -x -k "fused or block_orders or in_phase or golden or tall or geometry or carpet" > gpurun_out/r02_pytest_y.log 2>&1; echo "pytest rc=$?"; tail -n 3 gpurun_out/r02_pytest_y.log
+for n in 1 2 4 8; do
+if [ $n = 1 ]; then python bench.py --gpus 1 --steps 20 --warmup 5 > gpurun_out/r02_scale_n$n.json 2> gpurun_out/r02_scale_n$n.err; else
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2968$n bench.py --gpus $n --steps 20 --warmup 5 > gpurun_out/r02_scale_n$n.json 2> gpurun_out/r02_scale_n$n.err; fi; echo "bench$n rc=$?"
+python - <<PY
+import json
+for line in open("gpurun_out/r02_scale_n$n.json"):
+    if line.startswith("{"):
+        d=json.loads(line); print("N=$n", d["value"], d["ms_per_step"], "e2e", d["e2e"]["value"], "parity", d["parity"]["ok"], d["parity"]["c2"], "c4s", d["parity"]["c4s"].get("bitwise_equal"), "c4", d["c4"].get("value"), d.get("ib_share",{}).get("share"))
+PY
+done
