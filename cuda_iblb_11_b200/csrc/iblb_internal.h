@@ -26,7 +26,11 @@ __global__ void flux_reduce_v1(const double *qpart, int n, double *qacc, double 
                                const int *it_ptr, int it);
 __global__ void lb_init(const LbParams p, const double *rho_in, const double *u_in, double u0_amp,
                         int row0, int nrows);
+__global__ void lb_init_t(const LbParams p, const double *rho_in, const double *u_in, int row0,
+                          int nrows);
 __global__ void halo_push(const Lattice L, const double *buf, Remote left, Remote right);
+__global__ void lb_moments_t(const LbParams p, int streamed, int row0, int nrows, double *rho_out,
+                             double *u_out, double *force_out);
 __global__ void lb_moments(const LbParams p, int streamed, int row0, int nrows, double *rho_out,
                            double *u_out, double *f_out, double *force_out);
 __global__ void ib_coef(const int *k_of_j, float *coef, int mpc, int fine_points, int mucus);
@@ -95,6 +99,8 @@ struct iblb_solver {
     int cap_off;               // >= 0 while a graph batch is being captured: offset within the batch
     double *q_host;            // pinned: nq flux partial sums + the device error flag (one sync)
     double *stage_dev;         // kStageDoubles: row chunks of fields on their way to / from the host
+    cudaStream_t stream_copy;  // PCIe copies of one half of it while a kernel works on the other
+    cudaEvent_t ev_copy[2], ev_kern[2];
     int nq;
     bool flux_on;
     int xq_local;

@@ -190,22 +190,10 @@ __global__ void flux_reduce_v1(const double *qpart, int n, double *qacc, double 
 // in the reference layout (j = y*W + x) or, when null, rho = 1, u_x = u0_amp*sin(2pi(y+.5)/Y).
 // Rows [row0, row0 + nrows) per launch: rho_in / u_in hold that chunk only (plane stride W*nrows),
 // so that the host never needs a device copy of the whole field.
-__global__ void lb_init(const LbParams p, const double *rho_in, const double *u_in, double u0_amp,
-                        int row0, int nrows) {
+namespace {
+__device__ __forceinline__ void init_node(const LbParams &p, int x, int y, double rho, double ux,
+                                          double uy) {
     const Lattice &L = p.L;
-    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (gid >= (long long)L.W * nrows) return;
-    const int x = (int)(gid / nrows), y = row0 + (int)(gid - (long long)x * nrows);
-    double rho = 1.0, ux, uy = 0.0;
-    const double kTwoPi = 6.283185307179586476925286766559;
-    if (rho_in != nullptr) {
-        const long long j = (long long)(y - row0) * L.W + x, size = (long long)L.W * nrows;
-        rho = rho_in[j];
-        ux = u_in[j];
-        uy = u_in[size + j];
-    } else {
-        ux = u0_amp * sin(kTwoPi * (y + 0.5) / L.YDIM);
-    }
     const double w[9] = {kW0, kW1, kW1, kW1, kW1, kW2, kW2, kW2, kW2};
     const double cs2 = kCs * kCs;
     const long long c0 = L.off(x, y);
@@ -222,6 +210,58 @@ __global__ void lb_init(const LbParams p, const double *rho_in, const double *u_
             f0 += p.kforce * w[i] * (vx * p.gx + vy * p.gy);
         }
         p.dst[i * L.plane + c0] = f0;
+    }
+}
+}  // namespace
+
+// rho_in == nullptr: the initial state of main.cu:636-654 (one thread per node, y fastest)
+__global__ void lb_init(const LbParams p, const double *rho_in, const double *u_in, double u0_amp,
+                        int row0, int nrows) {
+    const Lattice &L = p.L;
+    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (long long)L.W * nrows) return;
+    const int x = (int)(gid / nrows), y = row0 + (int)(gid - (long long)x * nrows);
+    double rho = 1.0, ux, uy = 0.0;
+    const double kTwoPi = 6.283185307179586476925286766559;
+    if (rho_in != nullptr) {
+        const long long j = (long long)(y - row0) * L.W + x, size = (long long)L.W * nrows;
+        rho = rho_in[j];
+        ux = u_in[j];
+        uy = u_in[size + j];
+    } else {
+        ux = u0_amp * sin(kTwoPi * (y + 0.5) / L.YDIM);
+    }
+    init_node(p, x, y, rho, ux, uy);
+}
+
+// The same from host fields (iblb_set_fields): the inputs are x-fastest (reference layout), the
+// populations y-fastest, so a block transposes a 32x32 tile through shared memory and both sides
+// move in full sectors (the one-thread-per-node form read 8 bytes per 32-byte sector: 0.95 ms per
+// 128 MB chunk against 2.7 ms of PCIe copy, a quarter of the upload leg of e2e).
+// grid = (ceil(W/32), ceil(nrows/32)), block = 256.
+__global__ void __launch_bounds__(256) lb_init_t(const LbParams p, const double *rho_in,
+                                                 const double *u_in, int row0, int nrows) {
+    __shared__ double srho[32][33], sux[32][33], suy[32][33];
+    const Lattice &L = p.L;
+    const int tx0 = blockIdx.x * 32, ty0 = blockIdx.y * 32;
+    const int a = threadIdx.x & 31, b = threadIdx.x >> 5;
+    const long long size = (long long)L.W * nrows;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {  // rows of the chunk, x fastest
+        const int yl = ty0 + b + 8 * k, x = tx0 + a;
+        if (yl < nrows && x < L.W) {
+            const long long j = (long long)yl * L.W + x;
+            srho[b + 8 * k][a] = rho_in[j];
+            sux[b + 8 * k][a] = u_in[j];
+            suy[b + 8 * k][a] = u_in[size + j];
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 4; k++) {  // columns of the lattice, y fastest
+        const int x = tx0 + b + 8 * k, yl = ty0 + a;
+        if (yl < nrows && x < L.W)
+            init_node(p, x, row0 + yl, srho[a][b + 8 * k], sux[a][b + 8 * k], suy[a][b + 8 * k]);
     }
 }
 
@@ -247,17 +287,14 @@ __global__ void halo_push(const Lattice L, const double *buf, Remote left, Remot
 // buffer that iteration pulled from (still intact: the step wrote the other buffer).  Output in
 // the reference layouts.  `streamed` false = iteration 0 (no step yet): local moments.
 // Rows [row0, row0 + nrows) per launch, written to chunk-local arrays (plane stride W*nrows).
-__global__ void lb_moments(const LbParams p, int streamed, int row0, int nrows, double *rho_out,
-                           double *u_out, double *f_out, double *force_out) {
+namespace {
+// rho, u, force (and, f_wanted, the streamed populations) of node (x, y) as the reference's arrays
+// hold them after the last completed iteration
+__device__ __forceinline__ void moments_node(const LbParams &p, int streamed, int x, int y,
+                                             bool f_wanted, double (&f)[9], double &rho_o,
+                                             double &ux_o, double &uy_o, double &Fx, double &Fy) {
     const Lattice &L = p.L;
-    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long long size = (long long)L.W * nrows;
-    if (gid >= size) return;
-    // x fastest here so that the reference-layout stores coalesce
-    const int yl = (int)(gid / L.W), x = (int)(gid - (long long)yl * L.W);
-    const int y = row0 + yl;
     const long long P = L.plane;
-    double f[9];
 #pragma unroll
     for (int i = 0; i < 9; i++) {
         int pi = i, xs = x, ys = y;
@@ -274,7 +311,8 @@ __global__ void lb_moments(const LbParams p, int streamed, int row0, int nrows, 
         }
         f[i] = p.src[pi * P + L.off(xs, ys)];
     }
-    double Fx = 0., Fy = 0.;
+    Fx = 0.;
+    Fy = 0.;
     if (p.band != nullptr && y < p.band_rows) {
         Fx = p.band[(long long)x * p.band_ld + y];
         Fy = p.band[(long long)(L.W + x) * p.band_ld + y];
@@ -298,12 +336,10 @@ __global__ void lb_moments(const LbParams p, int streamed, int row0, int nrows, 
             uy = rmy / r;
             r = (rho - p.kforce * (ux * p.gx + uy * p.gy) * B) / (1. + (ux * ux + uy * uy) * A);
         }
-        if (rho_out) rho_out[gid] = r;
-        if (u_out) {
-            u_out[gid] = rmx / r;
-            u_out[size + gid] = rmy / r;
-        }
-        if (f_out) {
+        rho_o = r;
+        ux_o = rmx / r;
+        uy_o = rmy / r;
+        if (f_wanted) {
             const double w[9] = {kW0, kW1, kW1, kW1, kW1, kW2, kW2, kW2, kW2};
 #pragma unroll
             for (int i = 1; i < 9; i++) {
@@ -315,11 +351,27 @@ __global__ void lb_moments(const LbParams p, int streamed, int row0, int nrows, 
             }
         }
     } else {
-        if (rho_out) rho_out[gid] = rho;
-        if (u_out) {
-            u_out[gid] = (mx + p.half * (Fx + p.gx)) / rho;
-            u_out[size + gid] = (my + p.half * (Fy + p.gy)) / rho;
-        }
+        rho_o = rho;
+        ux_o = (mx + p.half * (Fx + p.gx)) / rho;
+        uy_o = (my + p.half * (Fy + p.gy)) / rho;
+    }
+}
+}  // namespace
+
+// one thread per node, x fastest: the form that also delivers the populations (tests, AoS [9*j+i])
+__global__ void lb_moments(const LbParams p, int streamed, int row0, int nrows, double *rho_out,
+                           double *u_out, double *f_out, double *force_out) {
+    const Lattice &L = p.L;
+    const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long size = (long long)L.W * nrows;
+    if (gid >= size) return;
+    const int yl = (int)(gid / L.W), x = (int)(gid - (long long)yl * L.W);
+    double f[9], rho, ux, uy, Fx, Fy;
+    moments_node(p, streamed, x, row0 + yl, f_out != nullptr, f, rho, ux, uy, Fx, Fy);
+    if (rho_out) rho_out[gid] = rho;
+    if (u_out) {
+        u_out[gid] = ux;
+        u_out[size + gid] = uy;
     }
     if (f_out) {
 #pragma unroll
@@ -328,6 +380,49 @@ __global__ void lb_moments(const LbParams p, int streamed, int row0, int nrows, 
     if (force_out) {
         force_out[gid] = Fx + p.gx;
         force_out[size + gid] = Fy + p.gy;
+    }
+}
+
+// rho, u, force only (iblb_get_fields / iblb_get_force): 32x32 tiles through shared memory — the
+// nodes are evaluated y fastest (the populations' layout), the results written x fastest (the
+// reference's), both in full sectors.  grid = (ceil(W/32), ceil(nrows/32)), block = 256.
+__global__ void __launch_bounds__(256) lb_moments_t(const LbParams p, int streamed, int row0,
+                                                    int nrows, double *rho_out, double *u_out,
+                                                    double *force_out) {
+    __shared__ double sv[5][32][33];
+    const Lattice &L = p.L;
+    const int tx0 = blockIdx.x * 32, ty0 = blockIdx.y * 32;
+    const int a = threadIdx.x & 31, b = threadIdx.x >> 5;
+    const long long size = (long long)L.W * nrows;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int x = tx0 + b + 8 * k, yl = ty0 + a;
+        if (yl < nrows && x < L.W) {
+            double f[9], rho, ux, uy, Fx, Fy;
+            moments_node(p, streamed, x, row0 + yl, false, f, rho, ux, uy, Fx, Fy);
+            sv[0][a][b + 8 * k] = rho;
+            sv[1][a][b + 8 * k] = ux;
+            sv[2][a][b + 8 * k] = uy;
+            sv[3][a][b + 8 * k] = Fx + p.gx;
+            sv[4][a][b + 8 * k] = Fy + p.gy;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int yl = ty0 + b + 8 * k, x = tx0 + a;
+        if (yl < nrows && x < L.W) {
+            const long long gid = (long long)yl * L.W + x;
+            if (rho_out) rho_out[gid] = sv[0][b + 8 * k][a];
+            if (u_out) {
+                u_out[gid] = sv[1][b + 8 * k][a];
+                u_out[size + gid] = sv[2][b + 8 * k][a];
+            }
+            if (force_out) {
+                force_out[gid] = sv[3][b + 8 * k][a];
+                force_out[size + gid] = sv[4][b + 8 * k][a];
+            }
+        }
     }
 }
 

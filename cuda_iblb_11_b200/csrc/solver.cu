@@ -119,9 +119,16 @@ IbParams make_ib_params(const iblb_solver *s, int src_idx, int slot) {
     return q;
 }
 
+// The staging buffer is used as two halves: while a kernel works on one (lb_init_t / lb_moments*),
+// the copy stream moves the other over PCIe.
 int stage_buffer(iblb_solver *s) {
     if (s->stage_dev) return IBLB_OK;
     IBLB_CUDA(cudaMalloc((void **)&s->stage_dev, sizeof(double) * kStageDoubles));
+    IBLB_CUDA(cudaStreamCreateWithFlags(&s->stream_copy, cudaStreamNonBlocking));
+    for (int h = 0; h < 2; h++) {
+        IBLB_CUDA(cudaEventCreateWithFlags(&s->ev_copy[h], cudaEventDisableTiming));
+        IBLB_CUDA(cudaEventCreateWithFlags(&s->ev_kern[h], cudaEventDisableTiming));
+    }
     return IBLB_OK;
 }
 
@@ -144,16 +151,26 @@ static int init_state(iblb_solver *s, const double *rho, const double *u) {
     } else {
         int rc = stage_buffer(s);
         if (rc) return rc;
-        const int rows = (int)std::max<size_t>(1, std::min<size_t>(Y, kStageDoubles / (3 * (size_t)W)));
-        for (int r0 = 0; r0 < Y; r0 += rows) {
+        const size_t half = kStageDoubles / 2;
+        const int rows = (int)std::max<size_t>(1, std::min<size_t>(Y, half / (3 * (size_t)W)));
+        cudaStream_t cp = s->stream_copy;
+        // the copies start behind whatever the main stream still does with the staging buffer
+        IBLB_CUDA(cudaEventRecord(s->ev_kern[0], s->stream));
+        IBLB_CUDA(cudaEventRecord(s->ev_kern[1], s->stream));
+        int h = 0;
+        for (int r0 = 0; r0 < Y; r0 += rows, h ^= 1) {
             const int nr = std::min(rows, Y - r0);
             const size_t cs = (size_t)W * nr, o = (size_t)W * r0;
-            double *d = s->stage_dev;
-            IBLB_CUDA(cudaMemcpyAsync(d, rho + o, sizeof(double) * cs, cudaMemcpyHostToDevice, s->stream));
-            IBLB_CUDA(cudaMemcpyAsync(d + cs, u + o, sizeof(double) * cs, cudaMemcpyHostToDevice, s->stream));
-            IBLB_CUDA(cudaMemcpyAsync(d + 2 * cs, u + size + o, sizeof(double) * cs, cudaMemcpyHostToDevice, s->stream));
-            lb_init<<<(unsigned)((cs + 255) / 256), 256, 0, s->stream>>>(q, d, d + cs, s->p.u0_amp, r0, nr);
+            double *d = s->stage_dev + h * half;
+            IBLB_CUDA(cudaStreamWaitEvent(cp, s->ev_kern[h], 0));  // the kernel that last read this half
+            IBLB_CUDA(cudaMemcpyAsync(d, rho + o, sizeof(double) * cs, cudaMemcpyHostToDevice, cp));
+            IBLB_CUDA(cudaMemcpyAsync(d + cs, u + o, sizeof(double) * cs, cudaMemcpyHostToDevice, cp));
+            IBLB_CUDA(cudaMemcpyAsync(d + 2 * cs, u + size + o, sizeof(double) * cs, cudaMemcpyHostToDevice, cp));
+            IBLB_CUDA(cudaEventRecord(s->ev_copy[h], cp));
+            IBLB_CUDA(cudaStreamWaitEvent(s->stream, s->ev_copy[h], 0));
+            lb_init_t<<<dim3((W + 31) / 32, (nr + 31) / 32), 256, 0, s->stream>>>(q, d, d + cs, r0, nr);
             IBLB_CUDA(cudaGetLastError());
+            IBLB_CUDA(cudaEventRecord(s->ev_kern[h], s->stream));
         }
     }
     // ghost columns of buffer 0 (own opposite edge, or the connected neighbours)
@@ -542,6 +559,14 @@ int iblb_destroy(iblb_solver *s) {
     cudaFree(s->buf[0]); cudaFree(s->buf[1]); cudaFree(s->qacc); cudaFree(s->qpart); cudaFree(s->qhist);
     if (s->q_host) cudaFreeHost(s->q_host);
     cudaFree(s->stage_dev);
+    if (s->stream_copy) {
+        cudaStreamSynchronize(s->stream_copy);
+        cudaStreamDestroy(s->stream_copy);
+        for (int h = 0; h < 2; h++) {
+            cudaEventDestroy(s->ev_copy[h]);
+            cudaEventDestroy(s->ev_kern[h]);
+        }
+    }
     cudaFree(s->flags); cudaFree(s->band); cudaFree(s->M.s); cudaFree(s->M.u_s);
     cudaFree(s->M.F_s); cudaFree(s->M.eps); cudaFree(s->M.bbox); cudaFree(s->coef);
     cudaFree(s->M.wx); cudaFree(s->M.wy); cudaFree(s->M.base);

@@ -468,30 +468,47 @@ static int run_moments(iblb_solver *s, double *rho, double *u, double *f, double
     const int W = s->L.W, Y = s->L.YDIM;
     const size_t size = (size_t)W * Y;
     const size_t per_node = (rho ? 1 : 0) + (u ? 2 : 0) + (f ? 9 : 0) + (force ? 2 : 0);
-    const int rows = (int)std::max<size_t>(1, std::min<size_t>(Y, kStageDoubles / (per_node * W)));
+    // two halves of the staging buffer: the kernel fills one while the copy stream drains the other
+    const size_t half = kStageDoubles / 2;
+    const int rows = (int)std::max<size_t>(1, std::min<size_t>(Y, half / (per_node * W)));
     const int streamed = s->it > 0;
     LbParams lp = make_lb_params(s, streamed ? (s->cur ^ 1) : s->cur);
     cudaError_t e = cudaSuccess;
     const cudaMemcpyKind D2H = cudaMemcpyDeviceToHost;
-    for (int r0 = 0; r0 < Y && e == cudaSuccess; r0 += rows) {
+    cudaStream_t cp = s->stream_copy;
+    int h = 0;
+    bool used[2] = {false, false};
+    for (int r0 = 0; r0 < Y && e == cudaSuccess; r0 += rows, h ^= 1) {
         const int nr = std::min(rows, Y - r0);
         const size_t cs = (size_t)W * nr, o = (size_t)W * r0, cb = sizeof(double) * cs;
-        double *d_rho = nullptr, *d_u = nullptr, *d_f = nullptr, *d_force = nullptr, *q = s->stage_dev;
+        double *d_rho = nullptr, *d_u = nullptr, *d_f = nullptr, *d_force = nullptr;
+        double *q = s->stage_dev + h * half;
         if (rho) { d_rho = q; q += cs; }
         if (u) { d_u = q; q += 2 * cs; }
         if (f) { d_f = q; q += 9 * cs; }
         if (force) { d_force = q; q += 2 * cs; }
-        lb_moments<<<(unsigned)((cs + 255) / 256), 256, 0, s->stream>>>(lp, streamed, r0, nr, d_rho,
-                                                                        d_u, d_f, d_force);
+        if (used[h]) e = cudaStreamWaitEvent(s->stream, s->ev_copy[h], 0);  // this half has been drained
+        if (e != cudaSuccess) break;
+        if (f)
+            lb_moments<<<(unsigned)((cs + 255) / 256), 256, 0, s->stream>>>(lp, streamed, r0, nr, d_rho,
+                                                                            d_u, d_f, d_force);
+        else
+            lb_moments_t<<<dim3((W + 31) / 32, (nr + 31) / 32), 256, 0, s->stream>>>(
+                lp, streamed, r0, nr, d_rho, d_u, d_force);
         e = cudaGetLastError();
-        if (e == cudaSuccess && rho) e = cudaMemcpyAsync(rho + o, d_rho, cb, D2H, s->stream);
-        if (e == cudaSuccess && u) e = cudaMemcpyAsync(u + o, d_u, cb, D2H, s->stream);
-        if (e == cudaSuccess && u) e = cudaMemcpyAsync(u + size + o, d_u + cs, cb, D2H, s->stream);
-        if (e == cudaSuccess && f) e = cudaMemcpyAsync(f + 9 * o, d_f, 9 * cb, D2H, s->stream);
-        if (e == cudaSuccess && force) e = cudaMemcpyAsync(force + o, d_force, cb, D2H, s->stream);
+        if (e == cudaSuccess) e = cudaEventRecord(s->ev_kern[h], s->stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(cp, s->ev_kern[h], 0);
+        if (e == cudaSuccess && rho) e = cudaMemcpyAsync(rho + o, d_rho, cb, D2H, cp);
+        if (e == cudaSuccess && u) e = cudaMemcpyAsync(u + o, d_u, cb, D2H, cp);
+        if (e == cudaSuccess && u) e = cudaMemcpyAsync(u + size + o, d_u + cs, cb, D2H, cp);
+        if (e == cudaSuccess && f) e = cudaMemcpyAsync(f + 9 * o, d_f, 9 * cb, D2H, cp);
+        if (e == cudaSuccess && force) e = cudaMemcpyAsync(force + o, d_force, cb, D2H, cp);
         if (e == cudaSuccess && force)
-            e = cudaMemcpyAsync(force + size + o, d_force + cs, cb, D2H, s->stream);
+            e = cudaMemcpyAsync(force + size + o, d_force + cs, cb, D2H, cp);
+        if (e == cudaSuccess) e = cudaEventRecord(s->ev_copy[h], cp);
+        used[h] = true;
     }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(cp);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
     if (e != cudaSuccess) return cuda_fail(e, "iblb_get_*");
     return IBLB_OK;
