@@ -1,12 +1,10 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -q --timeout 600 > gpurun_out/r02_pytest_gpu_u.log 2>&1; echo "pytest rc=$?"; tail -n 5 gpurun_out/r02_pytest_gpu_u.log
-IBLB_TAG=r02u bash tools/gpu_sanitize.sh | tail -7
-for k in 20 200; do
-python bench.py --steps $k --warmup 5 --no-cpu-baseline --no-extras > gpurun_out/r02u_bench_c2_$k.json 2> gpurun_out/r02u_bench_c2_$k.err; echo "bench rc=$?"
+for n in 8 2; do
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 2968$n bench.py --gpus $n --steps 20 --warmup 5 > gpurun_out/r02v_scale_n$n.json 2> gpurun_out/r02v_scale_n$n.err; echo "bench$n rc=$?"
 python - <<PY
 import json
-for line in open("gpurun_out/r02u_bench_c2_$k.json"):
+for line in open("gpurun_out/r02v_scale_n$n.json"):
     if line.startswith("{"):
-        d=json.loads(line); print("steps $k:", d["value"], d["ms_per_step"], "e2e", d["e2e"]["value"], d["parity"]["ok"])
+        d=json.loads(line); print("N=$n", d["value"], d["ms_per_step"], "e2e", d["e2e"]["value"], "parity", d["parity"]["ok"], "c4s", d["parity"]["c4s"].get("bitwise_equal"), "c4", d["c4"].get("value"))
 PY
 done
