@@ -40,6 +40,22 @@ __global__ void __launch_bounds__(256) copy1_v4(const double *src, double *dst, 
     for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < n4; g += (long long)gridDim.x * blockDim.x)
         st4(dst + 4 * g, ld4(src + 4 * g));
 }
+// in place: read nine planes, write the same addresses back (what an AA-pattern / esoteric-pull
+// LB step would do to HBM: one buffer, reads and writes in the same DRAM pages)
+__global__ void __launch_bounds__(256) inplace9_v4(double *buf, long long plane, long long n4) {
+    const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n4) return;
+    d4 v[9];
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+        asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(v[i].x), "=d"(v[i].y), "=d"(v[i].z), "=d"(v[i].w) : "l"(buf + i * plane + 4 * g));
+    }
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+        v[i].x += 1.;
+        st4(buf + i * plane + 4 * g, v[i]);
+    }
+}
 __global__ void read9_v4(const double *src, double *dst, long long plane, long long n4) {
     const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= n4) return;
@@ -60,7 +76,7 @@ int main() {
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
     const double bytes = 144.0 * nodes;
-    for (int variant = 0; variant < 4; variant++) {
+    for (int variant = 0; variant < 5; variant++) {
         float best = 1e9;
         for (int rep = 0; rep < 12; rep++) {
             cudaEventRecord(e0);
@@ -68,14 +84,16 @@ int main() {
             if (variant == 1) copy9_v4<<<(unsigned)((nodes / 4 + 255) / 256), 256>>>(a, b, plane, nodes / 4);
             if (variant == 2) copy1_v4<<<148 * 16, 256>>>(a, b, 9 * nodes / 4);
             if (variant == 3) read9_v4<<<(unsigned)((nodes / 4 + 255) / 256), 256>>>(a, b, plane, nodes / 4);
+            if (variant == 4) inplace9_v4<<<(unsigned)((nodes / 4 + 255) / 256), 256>>>(a, plane, nodes / 4);
             cudaEventRecord(e1);
             cudaEventSynchronize(e1);
             float ms;
             cudaEventElapsedTime(&ms, e0, e1);
             if (rep >= 2 && ms < best) best = ms;
         }
-        const char *names[4] = {"copy 9 planes, 128-bit, loads then stores", "copy 9 planes, 256-bit, loads then stores",
-                                "copy one stream, 256-bit, grid-stride", "read only 9 planes, 256-bit"};
+        const char *names[5] = {"copy 9 planes, 128-bit, loads then stores", "copy 9 planes, 256-bit, loads then stores",
+                                "copy one stream, 256-bit, grid-stride", "read only 9 planes, 256-bit",
+                                "in place 9 planes, 256-bit (read + write back)"};
         const double by = variant == 3 ? bytes / 2 : bytes;
         printf("%-45s %.4f ms  %.1f GB/s\n", names[variant], best, by / best / 1e6);
     }
