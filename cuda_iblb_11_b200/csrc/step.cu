@@ -2,6 +2,7 @@
 // (replace the D2H copies of main.cu:928, 944-982).
 #include <algorithm>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -605,3 +606,87 @@ int iblb_get_flux_history(iblb_solver *s, unsigned first_it, unsigned n, double 
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// iblb_get_fields_static: the field getter for callers that must not allocate device memory.
+//
+// iblb_get_fields stages its result in a 128 MB device buffer that it cudaMallocs on the first
+// call (stage_buffer, solver.cu).  That is no good for a host program which handed the whole GPU
+// to its own arena at start-up (a late cudaMalloc then fails at the first output interval, maybe
+// hours into a run), nor for one in which another host thread holds a stream capture open in the
+// global capture mode (the runtime refuses cudaMalloc from every thread while it lasts, and the
+// refusal breaks that capture).  Here the staging area is part of the library image instead: a
+// file-scope device array of fixed size, reserved on every GPU that loads libiblb.so from the
+// moment the module is loaded until the process exits.
+//
+// Host code must not hand `g_static_fields` itself to a kernel: in host code that name is a
+// host-side stand-in of the symbol, not a device address.  static_fields_ptr() asks the runtime for
+// the real address once per device (with that device current) and keeps it.
+namespace {
+
+// rho + u_x + u_y of the largest grid served: 3 * 2^18 doubles = 6 MiB per GPU
+constexpr size_t kStaticFieldNodes = IBLB_STATIC_FIELDS_MAX_NODES;
+static __device__ __align__(256) double g_static_fields[3 * kStaticFieldNodes];
+
+constexpr int kStaticMaxDevices = 64;
+double *g_static_ptr[kStaticMaxDevices];  // device address of g_static_fields on device d, or null
+std::mutex g_static_mu;
+
+// The caller has made `device` current.  The first call per device resolves the symbol (which may
+// also load this module onto the device); later calls return the stored address.
+int static_fields_ptr(int device, double **out) {
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    double *ptr = (device >= 0 && device < kStaticMaxDevices) ? g_static_ptr[device] : nullptr;
+    if (ptr == nullptr) {
+        const cudaError_t e = cudaGetSymbolAddress((void **)&ptr, g_static_fields);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_static_fields)");
+        if (ptr == nullptr) {
+            set_error("iblb_get_fields_static: the runtime returned no address for the staging array");
+            return IBLB_ECUDA;
+        }
+        if (device >= 0 && device < kStaticMaxDevices) g_static_ptr[device] = ptr;
+    }
+    *out = ptr;
+    return IBLB_OK;
+}
+
+}  // namespace
+
+extern "C" int iblb_get_fields_static(iblb_solver *s, double *rho, double *u) {
+    if (!s || (!rho && !u)) {
+        set_error("iblb_get_fields_static: null argument");
+        return IBLB_EINVAL;
+    }
+    const int W = s->L.W, Y = s->L.YDIM;
+    const size_t size = (size_t)W * Y;
+    if (size > kStaticFieldNodes) {
+        set_error("iblb_get_fields_static: " + std::to_string(W) + " x " + std::to_string(Y) + " = " +
+                  std::to_string(size) + " nodes exceed the fixed staging array of " +
+                  std::to_string(kStaticFieldNodes) +
+                  " nodes (IBLB_STATIC_FIELDS_MAX_NODES); use iblb_get_fields, which allocates");
+        return IBLB_EINVAL;
+    }
+    IBLB_CUDA(cudaSetDevice(s->device));
+    double *stage = nullptr;
+    {
+        int rc = static_fields_ptr(s->device, &stage);
+        if (rc == IBLB_OK) rc = check_device_flag(s);
+        if (rc == IBLB_OK) rc = materialise_ib(s);  // u needs the force band
+        if (rc) return rc;
+    }
+    // One launch over all rows.  The kernel writes every element that is copied out below, so the
+    // previous call's contents never show and nothing has to be cleared.
+    double *d_rho = rho ? stage : nullptr;
+    double *d_u = u ? stage + (rho ? size : 0) : nullptr;
+    const int streamed = s->it > 0;
+    const LbParams lp = make_lb_params(s, streamed ? (s->cur ^ 1) : s->cur);
+    lb_moments_t<<<dim3((W + 31) / 32, (Y + 31) / 32), 256, 0, s->stream>>>(lp, streamed, 0, Y, d_rho,
+                                                                          d_u, nullptr);
+    cudaError_t e = cudaGetLastError();
+    const size_t cb = sizeof(double) * size;
+    if (e == cudaSuccess && rho) e = cudaMemcpyAsync(rho, d_rho, cb, cudaMemcpyDeviceToHost, s->stream);
+    if (e == cudaSuccess && u) e = cudaMemcpyAsync(u, d_u, 2 * cb, cudaMemcpyDeviceToHost, s->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "iblb_get_fields_static");
+    return IBLB_OK;
+}

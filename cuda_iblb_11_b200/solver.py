@@ -108,7 +108,7 @@ SYMBOLS = [
     "iblb_last_step_launches", "iblb_profile_phases", "iblb_export_halo", "iblb_connect",
     "iblb_connect_local", "iblb_set_marker_replay", "iblb_run", "iblb_last_error", "iblb_version",
     "iblb_save_checkpoint", "iblb_load_checkpoint", "iblb_debug_violations", "iblb_run_gpus",
-    "iblb_device_count", "iblb_get_flux_history", "iblb_slab_range",
+    "iblb_device_count", "iblb_get_flux_history", "iblb_slab_range", "iblb_get_fields_static",
 ]
 
 
@@ -136,6 +136,7 @@ def lib():
     L.iblb_iteration.argtypes = [vp]
     L.iblb_iteration.restype = ctypes.c_uint
     L.iblb_get_fields.argtypes = [vp, vp, vp]
+    L.iblb_get_fields_static.argtypes = [vp, vp, vp]
     L.iblb_get_force.argtypes = [vp, vp]
     L.iblb_get_populations.argtypes = [vp, vp]
     L.iblb_get_markers.argtypes = [vp, vp, vp, vp, vp]
@@ -191,6 +192,14 @@ class Solver:
         rho = np.empty(self.size) if out_rho is None else out_rho
         u = np.empty(2 * self.size) if out_u is None else out_u
         _check(lib().iblb_get_fields(self._h, rho.ctypes.data, u.ctypes.data))
+        return rho, u
+
+    def fields_static(self, out_rho=None, out_u=None):
+        """fields() without any device allocation: staged through the library's fixed 6 MiB array
+        (iblb_get_fields_static; grids up to IBLB_STATIC_FIELDS_MAX_NODES nodes, IblbError beyond)."""
+        rho = np.empty(self.size) if out_rho is None else out_rho
+        u = np.empty(2 * self.size) if out_u is None else out_u
+        _check(lib().iblb_get_fields_static(self._h, rho.ctypes.data, u.ctypes.data))
         return rho, u
 
     def force(self):

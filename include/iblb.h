@@ -117,6 +117,27 @@ int iblb_get_force(iblb_solver *s, double *force /*2*size*/);
 int iblb_get_populations(iblb_solver *s, double *f);
 int iblb_get_markers(iblb_solver *s, float *pos, float *vel, float *force /*2*Ns each*/,
                      int *eps /*Ns*/);
+/* iblb_get_fields for callers that must not allocate device memory.  No counterpart in the
+ * reference (its main() allocates everything up front, main.cu:389-587, and copies straight out of
+ * those arrays); it exists because iblb_get_fields reserves its 128 MB device staging buffer with
+ * cudaMalloc on first use.  Two kinds of host program cannot live with that: one that gave all of
+ * the GPU's memory to its own arena at start-up, where a late cudaMalloc fails in the middle of a
+ * run; and one in which some other host thread keeps a stream capture open in the global capture
+ * mode, where the runtime refuses cudaMalloc from every thread and the refusal spoils that capture.
+ * This variant stages through a fixed array inside the library image (6 MiB on every GPU that loads
+ * libiblb.so, held until the process exits) and makes no cudaMalloc / cudaFree or other allocating
+ * call.  Same arguments, same values bit for bit, same error codes as iblb_get_fields, except:
+ *  - grids of more than IBLB_STATIC_FIELDS_MAX_NODES nodes (slab_w*YDIM for a slab) are refused
+ *    with IBLB_EINVAL and a message that names both sizes; C1, C3 and C5 (288x192, 576x192) fit;
+ *  - the first call on each device looks up the array's device address (and may make the runtime
+ *    load the library's device code there): make that first call before any stream capture begins;
+ *  - every call on a GPU, whichever solver it is for, goes through the same array.  A call returns
+ *    only when its copies have landed, so calls made one after another are safe; calls running at
+ *    the same time on one GPU from several host threads overwrite each other's data and must be
+ *    serialised by the caller.  Nothing in the array needs clearing between calls: each call
+ *    writes every value it reads back. */
+#define IBLB_STATIC_FIELDS_MAX_NODES 262144 /* 2^18 nodes, e.g. 1365 x 192 */
+int iblb_get_fields_static(iblb_solver *s, double *rho, double *u);
 /* cumulative flux Q of main.cu:928 / ImmersedBoundary.cu:259-264 */
 int iblb_get_flux(iblb_solver *s, double *Q);
 /* Q as it stood after each of the iterations first_it .. first_it+n-1 (0-based): the values the
