@@ -136,6 +136,18 @@ def compare_flux(a, b):
     pairs = [(float(x[1]), float(y[1])) for x, y in zip(ta, tb)
              if math.isfinite(float(x[1])) and math.isfinite(float(y[1]))]
     out["max_rel_diff_finite"] = max([abs(p - q) / max(abs(p), 1e-300) for p, q in pairs] or [0.0])
+    # per line (None where either side is non-finite), so that a failure says WHICH line moved.
+    # The last line is a different animal: the reference writes it after its loop from a host
+    # variable whose last asynchronous copy it never waits for (main.cu:1026-1034; every in-loop
+    # line waits on Q_done, main.cu:998), so it may show the flux of an earlier iteration.
+    out["rel_diff_per_line"] = [
+        abs(float(x[1]) - float(y[1])) / max(abs(float(x[1])), 1e-300)
+        if math.isfinite(float(x[1])) and math.isfinite(float(y[1])) else None
+        for x, y in zip(ta, tb)]
+    inloop = [d for d in out["rel_diff_per_line"][:-1] if d is not None]
+    out["max_rel_diff_in_loop_lines"] = max(inloop or [0.0])
+    out["reference_last_value"] = float(ta[-1][1]) if ta else None
+    out["ours_last_value"] = float(tb[-1][1]) if tb else None
     return out
 
 
