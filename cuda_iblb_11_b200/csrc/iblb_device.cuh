@@ -11,7 +11,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-// Development build (-DIBLB_CHECKED, `IBLB_CHECKED=1 python -m cuda_iblb_11_b200.build --force`): every
+// Development build (-DIBLB_CHECKED, `python -m cuda_iblb_11_b200.build --checked`): every
 // index the kernels form into the population buffers, the force band, the marker arrays and the
 // shared-memory tables is range-checked on the device; violations are counted per translation unit
 // and summed by iblb_debug_violations().  Stands in for compute-sanitizer, which is closed on the
@@ -48,6 +48,7 @@ constexpr int kSpreadTileX = 8, kSpreadTileY = 32;
 constexpr int kKinBatch = 32;      // iterations of marker kinematics computed per launch
 constexpr int kFluxHist = 4096;  // iterations of per-step flux the solver keeps (iblb_get_flux_history)
 constexpr int kSlabFlags = 4;  // slab step counters: [0],[1] data ready from the left / right neighbour; [2],[3] their release
+constexpr int kSlabPoison = 0x7fffffff;  // a flag word of a slab whose neighbour failed (above every step number)
 constexpr int kMaxLeftCilia = 16;  // r_max = 2*96/c_space (main.cu:185) must not exceed this
 
 struct Lattice {

@@ -49,7 +49,8 @@ size_t tile_step_smem_bytes();
 cudaError_t tile_step_prepare();  // once per device before the first launch
 __global__ void slab_wait(const volatile int *flags, int *rel_left, int *rel_right, int need,
                           long long timeout_ns, int *err);
-__global__ void slab_signal(int *left_flag, int *right_flag, int value);
+__global__ void slab_signal(int *left_flag, int *right_flag, int value, const int *err);
+__global__ void slab_unpoison(int *flags, int value);
 
 }  // namespace iblb
 
@@ -120,7 +121,7 @@ struct iblb_solver {
     int *nb_rel[2];            // left neighbour's flags[3], right neighbour's flags[2] (release)
     cudaStream_t stream_b;     // coupled slabs: wait -> boundary columns -> signal run here,
     cudaEvent_t ev_b, ev_i, ev_ib;  // beside the interior kernel on `stream` (events order them)
-    long long slab_timeout_ns; // bound on slab_wait's spin (IBLB_SLAB_TIMEOUT_S, default 60 s)
+    long long slab_timeout_ns; // bound on slab_wait's spin (IBLB_SLAB_TIMEOUT_S, default 900 s)
     void *nb_flag_mapped[2];
     bool self_left, self_right;
     int flag_base;             // step flags carry flag_base + it (monotonic across set_fields)

@@ -439,22 +439,44 @@ IBLB_CHECKED_COUNTER(checked_count_lb)
 // other GPUs, so both sides are always resident (never used between ranks that share a GPU).
 // The spin is bounded: when a neighbour never arrives (a rank died, or the ranks were asked for
 // different step counts) the kernel raises *err = 3 and falls through instead of hanging the GPU;
-// every later wait returns at once and the next getter / iblb_sync reports it.
+// every later wait returns at once and the next getter / iblb_sync reports it.  A slab in that
+// state no longer publishes step numbers: it writes kSlabPoison into its neighbours' release and
+// data-ready words, a neighbour's wait that finds the poison raises its own *err = 3 and passes it
+// on, so the failure travels round the ring one hop per step and EVERY rank reports it -- nobody
+// goes on computing with ghost columns that a failed slab filled from stale data.
+namespace {
+__device__ __forceinline__ void slab_fail(int *rel_left, int *rel_right, int *err) {
+    atomicExch(err, 3);
+    *reinterpret_cast<volatile int *>(rel_left) = kSlabPoison;
+    *reinterpret_cast<volatile int *>(rel_right) = kSlabPoison;
+    __threadfence_system();
+}
+}  // namespace
+
 __global__ void slab_wait(const volatile int *flags, int *rel_left, int *rel_right, int need,
                           long long timeout_ns, int *err) {
     if (threadIdx.x != 0) return;
+    if (*reinterpret_cast<volatile int *>(err) == 3) {
+        slab_fail(rel_left, rel_right, err);
+        return;
+    }
     *reinterpret_cast<volatile int *>(rel_left) = need;
     *reinterpret_cast<volatile int *>(rel_right) = need;
     __threadfence_system();
-    if (*reinterpret_cast<volatile int *>(err) == 3) return;
     unsigned long long t0, t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
     for (int i = 0; i < kSlabFlags; i++) {
-        while (flags[i] < need) {
+        for (;;) {
+            const int v = flags[i];
+            if (v == kSlabPoison) {  // that neighbour has failed
+                slab_fail(rel_left, rel_right, err);
+                return;
+            }
+            if (v >= need) break;
             __nanosleep(100);
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
             if ((long long)(t - t0) > timeout_ns) {
-                atomicExch(err, 3);
+                slab_fail(rel_left, rel_right, err);
                 return;
             }
         }
@@ -462,13 +484,21 @@ __global__ void slab_wait(const volatile int *flags, int *rel_left, int *rel_rig
     __threadfence_system();
 }
 
-__global__ void slab_signal(int *left_flag, int *right_flag, int value) {
+// `err`: this slab's error word; once it holds 3 the neighbours get the poison instead of a step number
+__global__ void slab_signal(int *left_flag, int *right_flag, int value, const int *err) {
     if (threadIdx.x == 0) {
+        if (*reinterpret_cast<const volatile int *>(err) == 3) value = kSlabPoison;
         __threadfence_system();  // the boundary kernel's peer stores are ordered before the flag
         *reinterpret_cast<volatile int *>(left_flag) = value;
         *reinterpret_cast<volatile int *>(right_flag) = value;
         __threadfence_system();
     }
+}
+
+// iblb_set_fields on a ring that had failed: every slab starts again from a common state, so a
+// poisoned word of this slab's own flags becomes the step number the new start expects
+__global__ void slab_unpoison(int *flags, int value) {
+    if (threadIdx.x < kSlabFlags && flags[threadIdx.x] == kSlabPoison) flags[threadIdx.x] = value;
 }
 
 }  // namespace iblb

@@ -232,7 +232,7 @@ int enqueue_iteration(iblb_solver *s, cudaStream_t st, bool graph_mode, PhaseEve
             IBLB_CUDA(cudaEventRecord(s->ev_boundary, st));
         } else {
             slab_signal<<<1, 32, 0, sb>>>(s->nb_flag[0], s->nb_flag[1],
-                                        s->flag_base + (int)s->it + 1);
+                                        s->flag_base + (int)s->it + 1, s->err_dev);
             launches += 1;
             if (two) IBLB_CUDA(cudaEventRecord(s->ev_b, sb));
         }
@@ -332,8 +332,9 @@ int check_device_flag(iblb_solver *s) {
                   : flag == 2 ? "ib_tile_lists: more markers touch a tile than kTileCap "
                                 "(use IBLB_FLAG_NO_FUSE)"
                               : "slab_wait timed out: a neighbouring slab never reached this "
-                                "iteration (rank lost, or ranks stepped different counts); the "
-                                "state of this slab is no longer valid");
+                                "iteration (rank lost, ranks stepped different counts, or host work "
+                                "between steps outlasted IBLB_SLAB_TIMEOUT_S), or a neighbour "
+                                "reported that failure; the state of this slab is no longer valid");
         return flag == 3 ? IBLB_ECUDA : IBLB_EINVAL;
     }
     return IBLB_OK;

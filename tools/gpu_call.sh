@@ -3,7 +3,8 @@
 #   gpurun --timeout 1500 -- 'bash tools/gpu_call.sh verify refprog sanitize small'
 # stages: verify   GPU suite + smoke + default bench (+ reference arm)
 #         refprog  the unmodified reference program vs ./app (tools/run_reference_program.py)
-#         sanitize compute-sanitizer memcheck + racecheck (tools/gpu_sanitize.sh)
+#         sanitize the range-checked build (-DIBLB_CHECKED: bounds checks on every device index, no race
+#                  detection) over every launch mode (tools/gpu_sanitize.sh; compute-sanitizer is closed here)
 #         small    per-step times of the cilia cases and the IB share (tools/time_small.py)
 #         ncu_c2 / ncu_c3   launch list + --set full capture of the dominant kernel
 TAG=${IBLB_TAG:-r02}
