@@ -9,6 +9,7 @@
 #include <chrono>
 #include <cmath>
 #include <condition_variable>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <deque>
@@ -174,6 +175,21 @@ struct Channel {
                 if (rc) return rc;
             }
         }
+        if (restart_path) {
+            // One file per slab: each file is complete or absent, but a run killed while save() was
+            // renaming can leave files of two different iterations side by side.  Slabs of
+            // different iterations must never be stepped together.
+            for (int r = 1; r < n_gpus; r++)
+                if (iblb_iteration(slab[r]) != iblb_iteration(slab[0])) {
+                    iblb::set_error("iblb_run: the checkpoint files " + std::string(restart_path) +
+                                    ".0 .. ." + std::to_string(n_gpus - 1) +
+                                    " are not one set: slab 0 is at iteration " +
+                                    std::to_string(iblb_iteration(slab[0])) + ", slab " +
+                                    std::to_string(r) + " at " + std::to_string(iblb_iteration(slab[r])) +
+                                    " (the run was stopped while it was saving; use an older set)");
+                    return IBLB_EINVAL;
+                }
+        }
         for (int r = 0; r < n_gpus; r++) {
             int rc = iblb_connect_local(slab[r], slab[(r + n_gpus - 1) % n_gpus], slab[(r + 1) % n_gpus]);
             if (rc) return rc;
@@ -235,9 +251,20 @@ struct Channel {
     }
     int save(const char *path) {
         if (slab.size() == 1) return iblb_save_checkpoint(slab[0], path);
+        // Two phases, so that the window in which the set is mixed is N renames and not N multi-GB
+        // writes: every slab first goes to <path>.<i>.new (iblb_save_checkpoint itself writes to a
+        // temporary and renames), and only when all of them are on disk do they replace the old
+        // set.  What is left of that window is caught on load (create() compares the iterations).
         for (size_t i = 0; i < slab.size(); i++) {
-            int rc = iblb_save_checkpoint(slab[i], (std::string(path) + "." + std::to_string(i)).c_str());
+            int rc = iblb_save_checkpoint(slab[i], (std::string(path) + "." + std::to_string(i) + ".new").c_str());
             if (rc) return rc;
+        }
+        for (size_t i = 0; i < slab.size(); i++) {
+            const std::string to = std::string(path) + "." + std::to_string(i), from = to + ".new";
+            if (rename(from.c_str(), to.c_str()) != 0) {
+                iblb::set_error("iblb_run: cannot rename " + from + " to " + to);
+                return IBLB_EIO;
+            }
         }
         return IBLB_OK;
     }

@@ -271,21 +271,47 @@ def test_run_on_several_gpus_writes_the_same_tree(tmp_path, n_slabs):
         del os.environ["IBLB_RESTART"]
     for sub, name in (("Raw/6/6", "40-fluid.dat"), ("Cilia/6/6", "40-cilia.dat")):
         assert open(os.path.join(one, sub, name)).read() == open(os.path.join(part, sub, name)).read()
+    # A run killed while it renames its per-slab files leaves files of two iterations side by side:
+    # such a set must be refused, not stepped.  Build one from two honest sets (iteration 20 / 40).
+    import shutil
+    from cuda_iblb_11_b200 import IblbError
+    assert not [f for f in os.listdir(str(tmp_path)) if f.endswith(".new")]
+    late = str(tmp_path / "late.ckp")
+    os.environ["IBLB_CHECKPOINT"] = late
+    try:
+        run(params(41), str(tmp_path / "late"), gpus=n_slabs)
+    finally:
+        del os.environ["IBLB_CHECKPOINT"]
+    shutil.copy("%s.%d" % (late, n_slabs - 1), "%s.%d" % (ck, n_slabs - 1))
+    os.environ["IBLB_RESTART"] = ck
+    try:
+        with pytest.raises(IblbError) as err:
+            run(params(41), str(tmp_path / "mixed"), gpus=n_slabs)
+    finally:
+        del os.environ["IBLB_RESTART"]
+    assert "not one set" in str(err.value)
 
 
 def test_app_runs_on_several_gpus_from_the_environment(tmp_path):
     app = os.path.join(ROOT, "app")
     if not os.path.exists(app):
         pytest.skip("app not built")
-    outs = []
-    for gpus in ("1", "2"):
-        env = dict(os.environ, IBLB_ROOT=str(tmp_path / ("D" + gpus)), IBLB_ITERATIONS="30",
-                   IBLB_GPUS=gpus)
-        r = subprocess.run([app] + "6 6 48 1.0 1.0 5 1.0 100 0 0".split(), capture_output=True,
-                           text=True, env=env)
-        assert r.returncode == 0, r.stderr
-        outs.append(open(str(tmp_path / ("D" + gpus) / "Flux" / "6_6_48_1_1x5-flux.dat")).read())
-    assert outs[0] == outs[1] and len(outs[0].splitlines()) >= 1
+    # 30 iterations with P_num = 100: INTERVAL = 30/100 = 0 (main.cu:301), so there is no periodic
+    # output and the flux file is the end-of-run line alone (main.cu:1030-1034); the reference
+    # itself cannot run this line (`it % INTERVAL`, main.cu:938, divides by zero).  200 iterations:
+    # INTERVAL = 2, a line at it = 0, 2, ... 198 (main.cu:996-1004) and the end-of-run line.
+    for iterations, lines in (("30", 1), ("200", 101)):
+        outs = []
+        for gpus in ("1", "2"):
+            root = tmp_path / ("D%s_%s" % (gpus, iterations))
+            env = dict(os.environ, IBLB_ROOT=str(root), IBLB_ITERATIONS=iterations, IBLB_GPUS=gpus)
+            r = subprocess.run([app] + "6 6 48 1.0 1.0 5 1.0 100 0 0".split(), capture_output=True,
+                               text=True, env=env)
+            assert r.returncode == 0, r.stderr
+            outs.append(open(str(root / "Flux" / "6_6_48_1_1x5-flux.dat")).read())
+        assert outs[0] == outs[1] and len(outs[0].splitlines()) == lines
+        if lines > 1:
+            assert outs[0].splitlines()[0].split() == ["0", "0"]  # it = 0: the fluid is still at rest
 
 
 def test_app_executable_surface(tmp_path):
