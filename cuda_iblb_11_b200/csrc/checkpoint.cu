@@ -139,7 +139,14 @@ int iblb_load_checkpoint(iblb_solver *s, const char *path) {
               fread(&reserved, 4, 1, fp) == 1 && fread(&pb, 8, 1, fp) == 1;
     if (!ok) {
         fclose(fp);
-        set_error(std::string("iblb_load_checkpoint: ") + path + " is not an IBLBCKP1 file of this build");
+        if (memcmp(magic, kMagic, 8) == 0 && psz != 0 && psz != sizeof(iblb_params))
+            // the layout after the magic starts with sizeof(iblb_params): a library whose parameter
+            // block has other fields (an older or newer libiblb) wrote this file
+            set_error(std::string("iblb_load_checkpoint: ") + path + " was written by another version of "
+                      "libiblb (its iblb_params has " + std::to_string(psz) + " bytes, this build's " +
+                      std::to_string(sizeof(iblb_params)) + "); checkpoints do not carry over between them");
+        else
+            set_error(std::string("iblb_load_checkpoint: ") + path + " is not an IBLBCKP1 checkpoint file");
         return IBLB_EINVAL;
     }
     if (!same_params(s->p, fp_params) || nq != s->nq || pb != pop_bytes(s) || (cur & ~1)) {
@@ -178,6 +185,8 @@ int iblb_load_checkpoint(iblb_solver *s, const char *path) {
     s->lists_base = -1;
     s->pdl_chain = false;
     s->ib_stale = s->p.c_num > 0 && it > 0;
+    // a loaded state clears an earlier device-side failure, as iblb_set_fields does
+    if (s->err_dev) IBLB_CUDA(cudaMemset(s->err_dev, 0, sizeof(int)));
     return IBLB_OK;
 }
 

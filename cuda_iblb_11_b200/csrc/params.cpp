@@ -16,7 +16,7 @@ void set_error(const std::string &msg) { g_error = msg; }
 extern "C" {
 
 const char *iblb_last_error(void) { return iblb::g_error.c_str(); }
-const char *iblb_version(void) { return "libiblb 0.1 (sm_100a)"; }
+const char *iblb_version(void) { return "libiblb 0.3 (sm_100a)"; }
 
 void iblb_params_default(iblb_params *p) {
     memset(p, 0, sizeof *p);

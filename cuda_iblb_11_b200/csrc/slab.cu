@@ -16,6 +16,14 @@ using namespace iblb;
 
 static_assert(sizeof(cudaIpcMemHandle_t) <= IBLB_IPC_HANDLE_BYTES, "IPC handle size");
 
+// the GPU behind ordinal `device` of this process
+static cudaError_t device_uuid(int device, unsigned char (&out)[16]) {
+    cudaDeviceProp prop;
+    const cudaError_t e = cudaGetDeviceProperties(&prop, device);
+    if (e == cudaSuccess) memcpy(out, prop.uuid.bytes, 16);
+    return e;
+}
+
 extern "C" {
 
 int iblb_export_halo(iblb_solver *s, iblb_halo_handle *h) {
@@ -35,11 +43,17 @@ int iblb_export_halo(iblb_solver *s, iblb_halo_handle *h) {
     h->width = (unsigned)s->L.W;
     h->device = s->device;
     h->pid = (int)getpid();
+    IBLB_CUDA(device_uuid(s->device, h->uuid));
     return IBLB_OK;
 }
 
 static int map_neighbour(iblb_solver *s, int face, const iblb_halo_handle *h) {
-    const bool self = (h->pid == (int)getpid() && h->device == s->device &&
+    // same GPU?  By identity: the exporter's ordinal is local to its process (CUDA_VISIBLE_DEVICES
+    // may list the GPUs in another order there, or show the same GPU under another number)
+    unsigned char mine[16];
+    IBLB_CUDA(device_uuid(s->device, mine));
+    const bool same_gpu = memcmp(mine, h->uuid, 16) == 0;
+    const bool self = (h->pid == (int)getpid() && same_gpu &&
                        h->plane == (unsigned long long)s->L.plane && h->width == (unsigned)s->L.W);
     // a handle exported by this very solver cannot be opened in its own process: use the pointers
     cudaIpcMemHandle_t own;
@@ -48,7 +62,7 @@ static int map_neighbour(iblb_solver *s, int face, const iblb_halo_handle *h) {
         if (cudaIpcGetMemHandle(&own, s->buf[0]) == cudaSuccess)
             is_own = memcmp(&own, h->mem[0], sizeof own) == 0;
     }
-    if (!is_own && h->device == s->device && h->pid != (int)getpid()) {
+    if (!is_own && same_gpu && h->pid != (int)getpid()) {
         // slab_wait spins until the neighbour's kernel has run: two processes time-slicing one GPU
         // can starve each other for ever
         set_error("iblb_connect: the neighbour is another process on the same GPU "

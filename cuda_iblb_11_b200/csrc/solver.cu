@@ -186,6 +186,12 @@ static int init_state(iblb_solver *s, const double *rho, const double *u) {
     s->lists_base = -1;
     s->flag_base += (int)s->it;  // all slabs reset together: later flag values stay above old ones
     s->it = 0;
+    // a new state clears an earlier device-side failure (tile-list overflow, slab timeout)
+    if (s->err_dev) IBLB_CUDA(cudaMemsetAsync(s->err_dev, 0, sizeof(int), s->stream));
+    if (s->flags) {
+        slab_unpoison<<<1, 32, 0, s->stream>>>(s->flags, s->flag_base);
+        IBLB_CUDA(cudaGetLastError());
+    }
     s->hist_from = 0;
     IBLB_CUDA(cudaStreamSynchronize(s->stream));
     return IBLB_OK;
@@ -257,7 +263,8 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
     }
     s->vec2 = (p.YDIM % 64 == 0);
     s->vec4 = true;
-    if (const char *e = getenv("IBLB_V4")) s->vec4 = atoi(e) != 0;  // development A/B
+    const bool dev_knobs = (p.flags & IBLB_FLAG_DEV_KNOBS) != 0;  // development A/B variables honoured
+    if (const char *e = dev_knobs ? getenv("IBLB_V4") : nullptr) s->vec4 = atoi(e) != 0;
     s->mpc = mpc;
     s->fine_points = fine_points;
     s->shape_scale = shape_scale;
@@ -287,8 +294,10 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
     TRY(cudaMalloc((void **)&s->it_dev, sizeof(int)));
     {
         const char *e = getenv("IBLB_SLAB_TIMEOUT_S");
-        const double sec = e ? atof(e) : 60.;
-        s->slab_timeout_ns = (long long)((sec > 0. ? sec : 60.) * 1e9);
+        // long enough for what a rank legitimately does between two steps while its neighbours
+        // wait (a multi-GB checkpoint with fsync, gathering and writing a BigData snapshot)
+        const double sec = e ? atof(e) : 900.;
+        s->slab_timeout_ns = (long long)((sec > 0. ? sec : 900.) * 1e9);
     }
     TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     TRY(cudaEventCreate(&s->ev0));
@@ -425,7 +434,7 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
                         s->tile_w = tw;
                     }
                 }
-                if (const char *e = getenv("IBLB_TILE_W")) {
+                if (const char *e = dev_knobs ? getenv("IBLB_TILE_W") : nullptr) {
                     const int v = atoi(e);
                     if (v == 6 || v == 8) s->tile_w = v;
                 }
@@ -440,7 +449,8 @@ int iblb_create(const iblb_params *pp, iblb_solver **out) {
                 if (cudaGetDeviceProperties(&prop, s->device) == cudaSuccess) sms = prop.multiProcessorCount;
                 const int rows = (L.YDIM / 64 > 8) ? s->band_tiles : L.YDIM / 64;
                 s->band_first = (long long)s->tiles_x * rows > sms ? 1 : 0;
-                if (const char *e = getenv("IBLB_BAND_FIRST")) s->band_first = atoi(e) != 0;
+                if (const char *e = dev_knobs ? getenv("IBLB_BAND_FIRST") : nullptr)
+                    s->band_first = atoi(e) != 0;
             }
             // Capacity of the per-tile plans, decided here and not at run time: an upper bound on
             // the markers / cilia that can ever be within 1.5 of a tile, from the per-marker

@@ -19,6 +19,7 @@ FLAG_PICK_HIGHEST_K = 2
 FLAG_NO_GRAPH = 4
 FLAG_NO_FUSE = 8
 FLAG_NO_PDL = 16
+FLAG_DEV_KNOBS = 64   # honour IBLB_V4 / IBLB_TILE_W / IBLB_BAND_FIRST (development A/B)
 FLAG_MUCUS = 32
 
 IPC_HANDLE_BYTES = 64
@@ -94,6 +95,7 @@ class HaloHandle(ctypes.Structure):
         ("plane", ctypes.c_ulonglong),
         ("ld", ctypes.c_uint), ("ghost", ctypes.c_uint), ("width", ctypes.c_uint),
         ("device", ctypes.c_int), ("pid", ctypes.c_int),
+        ("uuid", ctypes.c_ubyte * 16),
     ]
 
 

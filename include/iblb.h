@@ -50,6 +50,13 @@ extern "C" {
                                         MUCUS PRESENT" (main.cu:36-54, commented out there); default:
                                         the active "WITHOUT MUCUS" set (main.cu:56-74) */
 
+#define IBLB_FLAG_DEV_KNOBS 64u       /* development only: let the environment variables IBLB_V4,
+                                        IBLB_TILE_W and IBLB_BAND_FIRST override the kernel variant,
+                                        tile width and block order that iblb_create picks (A/B
+                                        measurements, tools/).  Without this flag they are ignored, so
+                                        that no stray variable changes what a production run launches;
+                                        results are bit-identical either way */
+
 typedef struct iblb_params {
     /* --- the ten driver arguments, main.cu:291-296 --- */
     unsigned c_fraction, c_num, c_space;
@@ -174,11 +181,20 @@ typedef struct iblb_halo_handle {
     unsigned char flag[IBLB_IPC_HANDLE_BYTES];   /* cudaIpcMemHandle_t of the step flags */
     unsigned long long plane;  /* doubles per population plane */
     unsigned ld, ghost, width; /* column pitch (doubles), ghost columns, owned columns */
-    int device, pid;
+    int device, pid;           /* exporter's CUDA ordinal (local to ITS process) and process id */
+    unsigned char uuid[16];    /* exporter's GPU (cudaDeviceProp::uuid): ordinals mean nothing across
+                                  processes whose CUDA_VISIBLE_DEVICES differ, this does */
 } iblb_halo_handle;
 /* Export this slab's buffers; import the left/right neighbours' (periodic ring).  After
  * iblb_connect the fused LB kernel stores its outgoing boundary columns straight into the
- * neighbours' ghost columns over NVLink and steps are ordered by device-side flags. */
+ * neighbours' ghost columns over NVLink and steps are ordered by device-side flags.
+ * A slab waits on the device for its neighbours for at most IBLB_SLAB_TIMEOUT_S seconds (environment,
+ * read by iblb_create; default 900): whatever a rank does on the host between two iblb_step calls
+ * while the others step on (checkpoints, snapshot files) must finish within that.  A slab that gives
+ * up marks its neighbours' flags, they mark theirs: within a few steps every rank's next getter or
+ * iblb_sync returns IBLB_ECUDA ("slab_wait timed out").  The run's state is then invalid on all ranks;
+ * iblb_set_fields on every rank (a collective restart) clears the condition when all ranks had been
+ * asked for the same number of steps; otherwise destroy the solvers and build the ring again. */
 int iblb_export_halo(iblb_solver *s, iblb_halo_handle *h);
 int iblb_connect(iblb_solver *s, const iblb_halo_handle *left, const iblb_halo_handle *right);
 /* Same-process variant (several solvers driven by one host thread, on one or several GPUs):

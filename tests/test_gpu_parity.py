@@ -25,7 +25,7 @@ import pytest
 
 from checkers import (REF_FLAG_HALF_FORCE_BODY, REF_FLAG_MUCUS, REF_FLAG_PICK_LOWEST_K, Checker,
                       make_params, reference_tau, rel_l2)
-from cuda_iblb_11_b200 import (FLAG_HALF_FORCE_BODY, FLAG_MUCUS, FLAG_NO_FUSE, FLAG_NO_GRAPH,
+from cuda_iblb_11_b200 import (FLAG_DEV_KNOBS, FLAG_HALF_FORCE_BODY, FLAG_MUCUS, FLAG_NO_FUSE, FLAG_NO_GRAPH,
                                FLAG_NO_PDL, FLAG_PICK_HIGHEST_K, Params, Solver)
 
 pytestmark = pytest.mark.gpu
@@ -142,7 +142,7 @@ def test_four_node_kernel_equals_pair_kernel(X, Y, flags, monkeypatch):
     """lb_fused_v4 (four nodes per thread, 256-bit loads and stores; rows in multiples of 128, no
     force band) against lb_fused_v2 (IBLB_V4=0): same device functions, same bits — fields,
     populations and the flux sum, whose reduction tree v4 reproduces — and both against the oracle."""
-    kw = dict(gx=2e-6, u0_amp=3e-3, flags=flags)
+    kw = dict(gx=2e-6, u0_amp=3e-3, flags=flags | FLAG_DEV_KNOBS)  # the variable counts only with it
     monkeypatch.setenv("IBLB_V4", "0")
     a = Solver(Params.channel(X, Y, **kw))
     monkeypatch.setenv("IBLB_V4", "1")

@@ -5,14 +5,14 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from cuda_iblb_11_b200 import Params, Solver
+from cuda_iblb_11_b200 import FLAG_DEV_KNOBS, Params, Solver
 
 X = Y = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
 res = {}
 for rep in range(3):
     for v in ("0", "1"):
         os.environ["IBLB_V4"] = v
-        s = Solver(Params.channel(X, Y, gx=1e-7))
+        s = Solver(Params.channel(X, Y, gx=1e-7, flags=FLAG_DEV_KNOBS))
         s.step(20)
         s.sync()
         s.step(100)

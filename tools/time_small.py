@@ -5,7 +5,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from cuda_iblb_11_b200 import FLAG_NO_FUSE, FLAG_NO_GRAPH, Params, Solver
+from cuda_iblb_11_b200 import FLAG_DEV_KNOBS, FLAG_NO_FUSE, FLAG_NO_GRAPH, Params, Solver
 
 
 def t_step(p, n, warm):
@@ -33,7 +33,7 @@ if __name__ == "__main__":
         tf = []
         for bf in ("0", "1"):
             os.environ["IBLB_BAND_FIRST"] = bf
-            tf.append(t_step(Params.channel(X, Y, **kw), n, 50))
+            tf.append(t_step(Params.channel(X, Y, flags=FLAG_DEV_KNOBS, **kw), n, 50))
         del os.environ["IBLB_BAND_FIRST"]
         print("      block order of lb_ib_tile_step: row tile fastest %.2f us, band tiles first %.2f us" %
               tuple(tf), flush=True)
