@@ -211,6 +211,18 @@ def make_solver(pl, wl, n_gpus):
     return s, p, nodes_total, Wl * w["Y"]
 
 
+def config_block(workload, X, Y, n, nodes_local):
+    """`config` of the JSON line, the same keys (and at N = 1 the same values) in both arms."""
+    w = WORKLOADS[workload]
+    return {"workload": "%s: %s" % (workload, w["desc"]),
+            "grid": [int(X), int(Y)], "columns_per_gpu": int(nodes_local // int(Y)),
+            "parallelism": ("1 GPU" if n == 1 else "%d independent replicas, one per GPU" % n
+                            if w["scaling"] == "replicas"
+                            else "x-slabs x%d, NVLink peer-store halos" % n),
+            "l2_policy": "working set %.1f GB per GPU >> 126 MB L2" % (nodes_local * 144 / 1e9)
+            if nodes_local * 144 > 1e9 else "L2-resident (latency-bound case)"}
+
+
 def _oracle():
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import checkers
@@ -252,6 +264,35 @@ def parity_c2(pl, s, p, steps_done, w):
             "rel_l2_rho": pl.max(e_rho), "rel_l2_ux": pl.max(e_ux), "max_abs_ux": pl.max(a_ux),
             "ux_rule": "rel L2 <= 1e-10 or max abs <= max(1e-16 x steps, 2e-14) (u is a difference of "
                        "O(0.1) populations)"}
+
+
+def parity_c2_moving(pl, w, steps=25, X=128):
+    """The C2 kernel on a channel that is NOT at rest (u0_amp = 1e-3, the profile of
+    tests/test_gpu_slabs_fullsize.py): here the relative bound on u means something, no absolute
+    floor.  Rank 0, a narrow channel of the full height (the forced channel is x-invariant)."""
+    if pl.rank != 0:
+        return None
+    from cuda_iblb_11_b200 import Params, Solver
+    Y = w["Y"]
+    s = Solver(Params.channel(X, Y, gx=w["gx"], u0_amp=1e-3, device=pl.local))
+    s.step(steps)
+    rho, u = s.fields()
+    s.close()
+    ck = _oracle()
+    o = ck.Checker("oracle", ck.make_params(4, Y, gx=w["gx"], u0_amp=1e-3, threads=os.cpu_count() or 1))
+    o.step(steps)
+    ro, uo = o.fields()
+    o.close()
+    rho, ux = rho.reshape(Y, X), u[:X * Y].reshape(Y, X)
+    x_inv = bool(np.array_equal(rho, np.broadcast_to(rho[:, :1], rho.shape)) and
+                 np.array_equal(ux, np.broadcast_to(ux[:, :1], ux.shape)))
+    pr, pu = ro.reshape(Y, 4)[:, 0], uo[:4 * Y].reshape(Y, 4)[:, 0]
+    e_rho = float(np.linalg.norm(rho[:, 0] - pr) / np.linalg.norm(pr))
+    e_ux = float(np.linalg.norm(ux[:, 0] - pu) / np.linalg.norm(pu))
+    return {"ok": bool(x_inv and e_rho <= 1e-10 and e_ux <= 1e-10),
+            "what": "%dx%d channel, u0_amp 1e-3, %d steps: exact x-invariance + column profile vs the "
+                    "oracle's 4x%d channel, rel L2 <= 1e-10 on rho and u_x, no absolute floor" % (X, Y, steps, Y),
+            "x_invariant": x_inv, "rel_l2_rho": e_rho, "rel_l2_ux": e_ux, "max_ux": float(np.abs(pu).max())}
 
 
 C4S = dict(X=4096, Y=1024, c_num=32, c_space=128, steps=40)  # down-scaled C4 for the self-check
@@ -348,23 +389,60 @@ def ib_share_leg(device, steps=4000):
     device time by events; share = (fused - pure) / fused."""
     from cuda_iblb_11_b200 import Params, Solver
     w = WORKLOADS["c3"]
-    res = {}
-    for name, kw in (("fused", dict(c_num=w["c_num"], c_space=w["c_space"], c_fraction=w["c_fraction"])),
-                     ("pure", dict(gx=1e-7))):
-        s = Solver(Params.channel(w["X"], w["Y"], device=device, **kw))
-        s.step(200)
-        s.sync()
-        best = 1e9
-        for _ in range(3):
-            s.step(steps)
+
+    def one(X, Y, c_num, c_space, c_fraction):
+        res = {}
+        for name, kw in (("fused", dict(c_num=c_num, c_space=c_space, c_fraction=c_fraction)),
+                         ("pure", dict(gx=1e-7))):
+            s = Solver(Params.channel(X, Y, device=device, **kw))
+            s.step(200)
             s.sync()
-            best = min(best, s.last_step_seconds / steps)
-        s.close()
-        res[name] = best * 1e6
-    return {"workload": "c3: " + w["desc"], "fused_us": round(res["fused"], 3),
-            "pure_lb_us": round(res["pure"], 3), "steps": steps,
-            "share": round((res["fused"] - res["pure"]) / res["fused"], 4),
+            best = 1e9
+            for _ in range(3):
+                s.step(steps)
+                s.sync()
+                best = min(best, s.last_step_seconds / steps)
+            s.close()
+            res[name] = best * 1e6
+        return {"grid": [X, Y], "cilia": c_num, "fused_us": round(res["fused"], 3),
+                "pure_lb_us": round(res["pure"], 3),
+                "share": round((res["fused"] - res["pure"]) / res["fused"], 4)}
+
+    c3 = one(w["X"], w["Y"], w["c_num"], w["c_space"], w["c_fraction"])
+    w1 = WORKLOADS["c1"]
+    others = [one(w1["X"], w1["Y"], w1["c_num"], w1["c_space"], w1["c_fraction"]),  # cilia6.sh grid
+              one(2304, 192, 48, 48, 48)]                                             # 4 x the cilia12.sh width
+    return {"workload": "c3: " + w["desc"], "fused_us": c3["fused_us"],
+            "pure_lb_us": c3["pure_lb_us"], "steps": steps, "share": c3["share"],
+            "other_grids": others,
             "how": "iblb_last_step_seconds of %d graph-replayed steps, best of 3, on two solvers" % steps}
+
+
+def c5_leg(pl, n, steps=4000, warmup=200):
+    """configs[4] (multiapp.sh:7-9, cilia6.sh:7-17 as one run per GPU): N independent replicas of the
+    cilia6.sh case, one per rank, no coupling; value = nodes of all replicas x steps / the slowest
+    rank's device time.  In-phase line of the sweep (the phase-lagged ones overflow within ~40
+    steps in the reference too; work per step is the same)."""
+    from cuda_iblb_11_b200 import Params, Solver
+    w = WORKLOADS["c1"]
+    s = Solver(Params.channel(w["X"], w["Y"], c_num=w["c_num"], c_space=w["c_space"],
+                              c_fraction=w["c_fraction"], device=pl.local))
+    s.step(warmup)
+    s.sync()
+    pl.barrier()
+    s.step(steps)
+    s.sync()
+    t = pl.max(s.last_step_seconds)
+    launches = int(pl.sum(float(s.last_step_launches)))
+    q = s.Q
+    finite = pl.min(1.0 if np.isfinite(q) else 0.0) == 1.0
+    pl.barrier()
+    s.close()
+    nodes = w["X"] * w["Y"] * n
+    return {"workload": "c5: %d replicas of %s" % (n, w["desc"]), "grid": [w["X"], w["Y"]],
+            "n_gpus": n, "scaling": "replicas", "value": round(nodes * steps / t / 1e6, 1),
+            "unit": "MLUPS", "us_per_step": round(1e6 * t / steps, 3), "steps": steps,
+            "warmup": warmup, "gpu_launches": launches, "flux_finite": bool(finite)}
 
 
 def run_ours(a):
@@ -462,7 +540,10 @@ def run_ours(a):
             "avg_launch_ms": round(1e3 * t_dev / a.steps, 4),
             "launches_of_kernel": lb_launches_per_rank,
             # ncu capture of this kernel on one GPU over the whole channel; not measured on slabs
-            "traffic": tr.get("dram_bytes_per_launch") if (tr and a.workload == "c2" and n == 1) else None}
+            "traffic": tr.get("dram_bytes_per_launch") if (tr and a.workload == "c2" and n == 1) else None,
+            # not measured in this run: read from a committed builder-run ncu capture of the same kernel
+            "traffic_source": ("profiles/roofline_traffic.json (builder-run ncu --set full capture, "
+                               "replayed here)") if (tr and a.workload == "c2" and n == 1) else None}
     out = None
     if pl.rank == 0:
         out = {
@@ -470,13 +551,7 @@ def run_ours(a):
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(1e3 * t / a.steps, 4),
             "higher_is_better": True, "scaling": WORKLOADS[a.workload]["scaling"],
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "%s: %s" % (a.workload, WORKLOADS[a.workload]["desc"]),
-                       "grid": [int(p.XDIM), int(p.YDIM)], "columns_per_gpu": nodes_local // int(p.YDIM),
-                       "parallelism": ("1 GPU" if n == 1 else "%d independent replicas, one per GPU" % n
-                                       if WORKLOADS[a.workload]["scaling"] == "replicas"
-                                       else "x-slabs x%d, NVLink peer-store halos" % n),
-                       "l2_policy": "working set %.1f GB per GPU >> 126 MB L2" % (nodes_local * 144 / 1e9)
-                       if nodes_local * 144 > 1e9 else "L2-resident (latency-bound case)"},
+            "config": config_block(a.workload, p.XDIM, p.YDIM, n, nodes_local),
             "gpu_launches": launches_total,
             "e2e": {"value": e2e_value, "unit": "MLUPS",
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
@@ -494,12 +569,23 @@ def run_ours(a):
         except Exception as e:
             c4s = {"ok": False, "error": "%s: %s" % (type(e).__name__, e)}
         parity = dict(parity or {}, c4s=c4s)
+        if a.workload == "c2":
+            try:
+                mv = parity_c2_moving(pl, WORKLOADS["c2"])
+            except Exception as e:
+                mv = {"ok": False, "error": "%s: %s" % (type(e).__name__, e)}
+            if mv is not None:
+                parity["c2_moving"] = mv
         parity["ok"] = all(v.get("ok", False) for v in parity.values() if isinstance(v, dict))
     if a.workload == "c2" and not a.no_extras:
         try:
             extras["c4"] = c4_leg(pl, n)
         except Exception as e:
             extras["c4"] = {"error": "%s: %s" % (type(e).__name__, e), "n_gpus": n}
+        try:
+            extras["c5"] = c5_leg(pl, n)
+        except Exception as e:
+            extras["c5"] = {"error": "%s: %s" % (type(e).__name__, e), "n_gpus": n}
         if n == 1:
             try:
                 extras["ib_share"] = ib_share_leg(pl.local)
@@ -584,7 +670,8 @@ def run_reference(a):
         "n_gpus": 1, "steps": steps, "warmup": warm, "ms_per_step": round(1e3 * t / steps, 4),
         "higher_is_better": True, "scaling": w["scaling"], "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": "%s: %s" % (a.workload, w["desc"]), "grid": [X, Y]},
+        # the reference is single-GPU whatever N the driver launches: its line describes one GPU
+        "config": config_block(a.workload, X, Y, 1, X * Y),
         "gpu_launches": launches,
         "cpu_baseline": {"value": round(value, 2), "unit": "MLUPS", "cores": cores,
                          "kind": "reference", "sample": sample + "; the reference has no CPU path"},

@@ -7,7 +7,9 @@
 #                  detection) over every launch mode (tools/gpu_sanitize.sh; compute-sanitizer is closed here)
 #         small    per-step times of the cilia cases and the IB share (tools/time_small.py)
 #         ncu_c2 / ncu_c3   launch list + --set full capture of the dominant kernel
-TAG=${IBLB_TAG:-r02}
+#         ncu_markers       --set full capture of the marker-side and host-buffer kernels
+#         driver_bench      both bench arms with the driver's arguments (--gpus 1 --steps 20 --warmup 5)
+TAG=${IBLB_TAG:-r03}
 mkdir -p gpurun_out
 for stage in "$@"; do
   case $stage in
@@ -41,6 +43,18 @@ for stage in "$@"; do
         python bench.py --workload c3 --steps 64 --warmup 64 --no-cpu-baseline > gpurun_out/${TAG}_c3_ncu_launches.out 2>&1
       ncu --set full --clock-control none --cache-control none --import-source on -k regex:lb_ib -s 40 -c 2 -o gpurun_out/${TAG}_lb_ib_full -f \
         python bench.py --workload c3 --steps 64 --warmup 64 --no-cpu-baseline > gpurun_out/${TAG}_c3_ncu_full.out 2>&1
+      ;;
+    ncu_markers)
+      python tools/ncu_marker_kernels.py > gpurun_out/${TAG}_ncu_markers_plain.out 2>&1; echo "plain rc=$?"
+      ncu --set full --clock-control none --import-source on \
+        -k regex:"ib_kinematics_batch|ib_tile_lists|ib_interp|ib_spread|lb_init_t|lb_moments_t" -c 24 \
+        -o gpurun_out/${TAG}_marker_kernels_full -f python tools/ncu_marker_kernels.py > gpurun_out/${TAG}_ncu_markers.out 2>&1; echo "ncu rc=$?"
+      tail -n 3 gpurun_out/${TAG}_ncu_markers.out
+      ;;
+    driver_bench)
+      python bench.py --impl reference --gpus 1 --steps 20 --warmup 5 > gpurun_out/${TAG}_bench_ref_driver.json 2> gpurun_out/${TAG}_bench_ref_driver.err; echo "ref rc=$?"
+      python bench.py --gpus 1 --steps 20 --warmup 5 > gpurun_out/${TAG}_bench_driver.json 2> gpurun_out/${TAG}_bench_driver.err; echo "bench rc=$?"
+      cut -c1-6000 gpurun_out/${TAG}_bench_driver.json; tail -n 5 gpurun_out/${TAG}_bench_driver.err
       ;;
     *) echo "unknown stage $stage";;
   esac
